@@ -1,0 +1,264 @@
+"""TEST INFRASTRUCTURE (oracle) -- ctypes front-ends for the two CPU checkers.
+
+  Port  -> oracle/_build/libopb_oracle.so  (post_oracle.c, our plain-C restatement)
+  Ref   -> oracle/_ref/libopref_post.so    (the reference's own object code + ref_shim.cpp)
+
+Only tests/, __graft_entry__.smoke() and bench.py (cpu_baseline / --impl reference) may import this.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+PORT_SO = os.path.join(_HERE, "_build", "libopb_oracle.so")
+REF_SO = os.path.join(_HERE, "_ref", "libopref_post.so")
+
+BODY_25, COCO_18 = 0, 1
+MODE_CPU, MODE_CUDA = 0, 1
+MAX_PEAKS = 127  # POSE_MAX_PEOPLE, include/openpose/pose/poseParameters.hpp:14
+
+_f32p = C.POINTER(C.c_float)
+_i32p = C.POINTER(C.c_int)
+
+
+def build(ref: bool = True) -> None:
+    """Compile the checkers (oracle/Makefile). The _ref target is a no-op without /root/reference."""
+    subprocess.check_call(["make", "-s", "-C", _HERE, "oracle"] + (["ref"] if ref else []))
+
+
+def _fp(a: np.ndarray):
+    assert a.dtype == np.float32 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(_f32p)
+
+
+def _ip(a: Optional[np.ndarray]):
+    if a is None:
+        return None
+    assert a.dtype == np.int32 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(_i32p)
+
+
+def model_dims(model: int) -> Tuple[int, int]:
+    """(number of body parts, number of limbs/PAF pairs)."""
+    return {BODY_25: (25, 26), COCO_18: (18, 19)}[model]
+
+
+def pose_defaults(model: int, maximize_positives: bool = False) -> dict:
+    """src/openpose/pose/poseParameters.cpp:677-756 (restated; checked against Ref in the tests)."""
+    mp = maximize_positives
+    return dict(nms_threshold=0.02 if mp else 0.05, inter_min_above=0.75 if mp else 0.95,
+                inter_threshold=0.01 if mp else 0.05, min_subset_cnt=2 if mp else 3,
+                min_subset_score=0.05 if mp else 0.4)
+
+
+class Port:
+    """Our C restatement (post_oracle.c)."""
+
+    def __init__(self):
+        if not os.path.exists(PORT_SO):
+            build(ref=False)
+        L = self.lib = C.CDLL(PORT_SO)
+        L.opo_nms.restype = C.c_int
+        L.opo_nms.argtypes = [_f32p, _f32p, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
+                              C.c_float, C.c_int]
+        L.opo_resize_merge.restype = None
+        L.opo_resize_merge.argtypes = [_f32p, C.POINTER(_f32p), _i32p, _i32p, _f32p, _f32p, C.c_int, C.c_int,
+                                       C.c_int, C.c_int]
+        L.opo_maximum.restype = None
+        L.opo_maximum.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int]
+        L.opo_pair_scores.restype = None
+        L.opo_pair_scores.argtypes = [_f32p, _f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
+                                      C.c_float, C.c_float, C.c_int]
+        L.opo_connect_cpu.restype = C.c_int
+        L.opo_connect_cpu.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
+                                      C.c_int, C.c_float, C.c_float, C.c_float, C.c_int, _f32p, _f32p, _i32p,
+                                      C.c_int]
+        L.opo_connect_from_pair_scores.restype = C.c_int
+        L.opo_connect_from_pair_scores.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_float,
+                                                   C.c_float, C.c_int, _f32p, _f32p, _i32p, C.c_int]
+
+    def nms(self, heat: np.ndarray, thr: float, channels: int, off=(0.5, 0.5), max_peaks=MAX_PEAKS,
+            mode=MODE_CPU, peaks: Optional[np.ndarray] = None) -> np.ndarray:
+        """heat (C>=channels, H, W) -> peaks (channels, max_peaks+1, 3). Rows beyond count keep `peaks`' content."""
+        heat = np.ascontiguousarray(heat, np.float32)
+        _, h, w = heat.shape
+        if peaks is None:
+            peaks = np.zeros((channels, max_peaks + 1, 3), np.float32)
+        rc = self.lib.opo_nms(_fp(peaks), _fp(heat), thr, channels, h, w, max_peaks, off[0], off[1], mode)
+        if rc:
+            raise ValueError("threshold value invalid.")
+        return peaks
+
+    def resize_merge(self, srcs: Sequence[np.ndarray], ht: int, wt: int,
+                     scale_ratios: Optional[Sequence[float]] = None) -> np.ndarray:
+        """srcs[i] (C, h_i, w_i) -> (C, ht, wt); scale factors per resizeAndMergeBase.cu:379-380,475-477."""
+        srcs = [np.ascontiguousarray(s, np.float32) for s in srcs]
+        n = len(srcs)
+        c = srcs[0].shape[0]
+        sw, sh = scale_factors([s.shape for s in srcs], ht, wt, scale_ratios)
+        hs = np.array([s.shape[1] for s in srcs], np.int32)
+        ws = np.array([s.shape[2] for s in srcs], np.int32)
+        ptrs = (_f32p * n)(*[_fp(s) for s in srcs])
+        dst = np.empty((c, ht, wt), np.float32)
+        self.lib.opo_resize_merge(_fp(dst), ptrs, _ip(hs), _ip(ws), _fp(sw), _fp(sh), n, c, ht, wt)
+        return dst
+
+    def maximum(self, heat: np.ndarray, parts: int) -> np.ndarray:
+        heat = np.ascontiguousarray(heat, np.float32)
+        _, h, w = heat.shape
+        out = np.empty((parts, 3), np.float32)
+        self.lib.opo_maximum(_fp(out), _fp(heat), parts, h, w)
+        return out
+
+    def pair_scores(self, heat, peaks, model, p=None, max_peaks=MAX_PEAKS, mode=MODE_CPU) -> np.ndarray:
+        p = p or pose_defaults(model)
+        heat = np.ascontiguousarray(heat, np.float32)
+        peaks = np.ascontiguousarray(peaks, np.float32)
+        _, h, w = heat.shape
+        cube = np.empty((model_dims(model)[1], max_peaks, max_peaks), np.float32)
+        self.lib.opo_pair_scores(_fp(cube), _fp(heat), _fp(peaks), model, w, h, max_peaks,
+                                 p["inter_threshold"], p["inter_min_above"], p["nms_threshold"], mode)
+        return cube
+
+    def connect(self, heat, peaks, model, p=None, scale=1.0, maximize_positives=False, max_peaks=MAX_PEAKS,
+                capacity=1024):
+        """connectBodyPartsCpu -> (keypoints (P, parts, 3), scores (P,), rows (P, parts+1) int32)."""
+        p = p or pose_defaults(model, maximize_positives)
+        heat = np.ascontiguousarray(heat, np.float32)
+        peaks = np.ascontiguousarray(peaks, np.float32)
+        _, h, w = heat.shape
+        parts = model_dims(model)[0]
+        kp = np.zeros((capacity, parts, 3), np.float32)
+        sc = np.zeros((capacity,), np.float32)
+        rows = np.zeros((capacity, parts + 1), np.int32)
+        n = self.lib.opo_connect_cpu(_fp(heat), _fp(peaks), model, w, h, max_peaks, p["inter_min_above"],
+                                     p["inter_threshold"], int(p["min_subset_cnt"]), p["min_subset_score"],
+                                     p["nms_threshold"], scale, int(maximize_positives), _fp(kp), _fp(sc),
+                                     _ip(rows), capacity)
+        assert 0 <= n <= capacity, n
+        return kp[:n].copy(), sc[:n].copy(), rows[:n].copy()
+
+    def connect_from_pair_scores(self, cube, peaks, model, p=None, scale=1.0, maximize_positives=False,
+                                 max_peaks=MAX_PEAKS, capacity=1024):
+        p = p or pose_defaults(model, maximize_positives)
+        cube = np.ascontiguousarray(cube, np.float32)
+        peaks = np.ascontiguousarray(peaks, np.float32)
+        parts = model_dims(model)[0]
+        kp = np.zeros((capacity, parts, 3), np.float32)
+        sc = np.zeros((capacity,), np.float32)
+        rows = np.zeros((capacity, parts + 1), np.int32)
+        n = self.lib.opo_connect_from_pair_scores(_fp(cube), _fp(peaks), model, max_peaks,
+                                                  int(p["min_subset_cnt"]), p["min_subset_score"], scale,
+                                                  int(maximize_positives), _fp(kp), _fp(sc), _ip(rows), capacity)
+        assert 0 <= n <= capacity, n
+        return kp[:n].copy(), sc[:n].copy(), rows[:n].copy()
+
+
+def scale_factors(shapes, ht: int, wt: int, scale_ratios=None):
+    """FP32 scaleWidths/scaleHeights exactly as resizeAndMergeBase.cu:379-380,475-477 computes them."""
+    n = len(shapes)
+    ratios = np.asarray(scale_ratios if scale_ratios is not None else [1.0] * n, np.float32)
+    w0, h0 = shapes[0][-1], shapes[0][-2]
+    main_w = np.float32(wt) / np.float32(w0)
+    main_h = np.float32(ht) / np.float32(h0)
+    sw = np.empty(n, np.float32)
+    sh = np.empty(n, np.float32)
+    for i in range(n):
+        r = np.float32(ratios[i] / ratios[0])
+        sw[i] = main_w / r
+        sh[i] = main_h / r
+    return sw, sh
+
+
+class Ref:
+    """The reference's own object code (nmsCpu / connectBodyPartsCpu / pafPtrIntoVector...)."""
+
+    def __init__(self):
+        if not os.path.exists(REF_SO):
+            if os.path.exists("/root/reference/src/openpose/net/nmsBase.cpp"):
+                build(ref=True)
+            if not os.path.exists(REF_SO):
+                raise FileNotFoundError(REF_SO)
+        L = self.lib = C.CDLL(REF_SO)
+        L.ref_last_error.restype = C.c_char_p
+        L.ref_nms_cpu.restype = C.c_int
+        L.ref_nms_cpu.argtypes = [_f32p, _i32p, _f32p, C.c_float, _i32p, _i32p, C.c_float, C.c_float]
+        L.ref_connect_cpu.restype = C.c_int
+        L.ref_connect_cpu.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
+                                      C.c_int, C.c_float, C.c_float, C.c_float, C.c_int, _f32p, _f32p, C.c_int]
+        L.ref_connect_from_pair_scores.restype = C.c_int
+        L.ref_connect_from_pair_scores.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_float,
+                                                   C.c_float, C.c_int, _f32p, _f32p, C.c_int]
+        L.ref_pose_part_pairs.argtypes = [C.c_int, C.POINTER(C.c_uint), C.c_int]
+        L.ref_pose_map_index.argtypes = [C.c_int, C.POINTER(C.c_uint), C.c_int]
+        L.ref_pose_defaults.argtypes = [C.c_int, C.c_int, _f32p]
+        L.ref_pose_defaults.restype = None
+
+    @staticmethod
+    def available() -> bool:
+        return os.path.exists(REF_SO) or os.path.exists("/root/reference/src/openpose/net/nmsBase.cpp")
+
+    def nms(self, heat, thr, channels, off=(0.5, 0.5), max_peaks=MAX_PEAKS, peaks=None) -> np.ndarray:
+        heat = np.ascontiguousarray(heat, np.float32)
+        _, h, w = heat.shape
+        if peaks is None:
+            peaks = np.zeros((channels, max_peaks + 1, 3), np.float32)
+        kernel = np.zeros((channels, h, w), np.int32)
+        tsz = np.array([1, channels, max_peaks + 1, 3], np.int32)
+        ssz = np.array([1, heat.shape[0], h, w], np.int32)
+        rc = self.lib.ref_nms_cpu(_fp(peaks), _ip(kernel), _fp(heat), thr, _ip(tsz), _ip(ssz), off[0], off[1])
+        if rc:
+            raise ValueError(self.lib.ref_last_error().decode())
+        return peaks
+
+    def connect(self, heat, peaks, model, p=None, scale=1.0, maximize_positives=False, max_peaks=MAX_PEAKS,
+                capacity=1024):
+        p = p or pose_defaults(model, maximize_positives)
+        heat = np.ascontiguousarray(heat, np.float32)
+        peaks = np.ascontiguousarray(peaks, np.float32)
+        _, h, w = heat.shape
+        parts = model_dims(model)[0]
+        kp = np.zeros((capacity, parts, 3), np.float32)
+        sc = np.zeros((capacity,), np.float32)
+        n = self.lib.ref_connect_cpu(_fp(heat), _fp(peaks), model, w, h, max_peaks, p["inter_min_above"],
+                                     p["inter_threshold"], int(p["min_subset_cnt"]), p["min_subset_score"],
+                                     p["nms_threshold"], scale, int(maximize_positives), _fp(kp), _fp(sc),
+                                     capacity)
+        if n < 0:
+            raise RuntimeError(self.lib.ref_last_error().decode())
+        assert n <= capacity
+        return kp[:n].copy(), sc[:n].copy()
+
+    def connect_from_pair_scores(self, cube, peaks, model, p=None, scale=1.0, maximize_positives=False,
+                                 max_peaks=MAX_PEAKS, capacity=1024):
+        p = p or pose_defaults(model, maximize_positives)
+        cube = np.ascontiguousarray(cube, np.float32)
+        peaks = np.ascontiguousarray(peaks, np.float32)
+        parts = model_dims(model)[0]
+        kp = np.zeros((capacity, parts, 3), np.float32)
+        sc = np.zeros((capacity,), np.float32)
+        n = self.lib.ref_connect_from_pair_scores(_fp(cube), _fp(peaks), model, max_peaks,
+                                                  int(p["min_subset_cnt"]), p["min_subset_score"], scale,
+                                                  int(maximize_positives), _fp(kp), _fp(sc), capacity)
+        if n < 0:
+            raise RuntimeError(self.lib.ref_last_error().decode())
+        return kp[:n].copy(), sc[:n].copy()
+
+    def tables(self, model: int):
+        buf = (C.c_uint * 512)()
+        n = self.lib.ref_pose_part_pairs(model, buf, 512)
+        pairs = list(buf[:n])
+        n = self.lib.ref_pose_map_index(model, buf, 512)
+        mapidx = list(buf[:n])
+        return pairs, mapidx
+
+    def defaults(self, model: int, maximize_positives: bool = False) -> dict:
+        out = np.zeros(5, np.float32)
+        self.lib.ref_pose_defaults(model, int(maximize_positives), _fp(out))
+        return dict(nms_threshold=float(out[0]), inter_min_above=float(out[1]), inter_threshold=float(out[2]),
+                    min_subset_cnt=int(out[3]), min_subset_score=float(out[4]))

@@ -1,0 +1,241 @@
+// TEST INFRASTRUCTURE (oracle) -- never linked into the product.
+//
+// Link shim that lets the reference's own, UNMODIFIED post-processing sources
+//   /root/reference/src/openpose/net/nmsBase.cpp
+//   /root/reference/src/openpose/net/bodyPartConnectorBase.cpp
+//   /root/reference/src/openpose/pose/poseParameters.cpp   (+ point, rectangle, errorAndLog, string)
+// be built into oracle/_ref/libopref_post.so without OpenCV (see oracle/Makefile).
+// It supplies
+//   (1) the six op::Array<T> members those objects leave undefined (the reference defines them
+//       in src/openpose/core/array.cpp:100-118,283-338,421-440,641-708, which needs OpenCV),
+//   (2) op::Matrix's default constructor (src/openpose/core/matrix.cpp, needs OpenCV),
+//   (3) op::getKeypointsRoi(Rectangle,Rectangle) (src/openpose/utilities/keypoint.cpp:587-640;
+//       only reachable for >=135-part models, which are out of scope -> aborts),
+//   (4) a plain C entry surface (ref_*) so Python (ctypes) can drive the reference functions.
+// Nothing here restates reference arithmetic: nms / PAF scoring / assembly all run in the
+// reference's own object code.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <functional>
+#include <numeric>
+#include <openpose/core/array.hpp>
+#include <openpose/core/matrix.hpp>
+#include <openpose/core/point.hpp>
+#include <openpose/core/rectangle.hpp>
+#include <openpose/net/bodyPartConnectorBase.hpp>
+#include <openpose/net/nmsBase.hpp>
+#include <openpose/pose/poseParameters.hpp>
+
+namespace op
+{
+    // (2) Matrix(): an empty handle is all Array<T> needs.
+    Matrix::Matrix() {}
+
+    // (1) Array<T> members. Storage semantics: row-major, owned by a shared_ptr<T[]>.
+    template<typename T>
+    void Array<T>::reset(const std::vector<int>& sizes)
+    {
+        if (sizes.empty())
+        {
+            mSize.clear();
+            mVolume = 0;
+            spData.reset();
+            pData = nullptr;
+            return;
+        }
+        mSize = sizes;
+        mVolume = 1;
+        for (const auto s : sizes)
+            mVolume *= (size_t)s;
+        spData.reset(new T[mVolume], std::default_delete<T[]>());
+        pData = spData.get();
+    }
+
+    template<typename T>
+    void Array<T>::reset(const int size)
+    {
+        if (size > 0)
+            reset(std::vector<int>{size});
+        else
+            reset(std::vector<int>{});
+    }
+
+    template<typename T>
+    void Array<T>::reset(const std::vector<int>& sizes, const T value)
+    {
+        reset(sizes);
+        for (size_t i = 0; i < mVolume; i++)
+            pData[i] = value;
+    }
+
+    template<typename T>
+    Array<T>::Array(const std::vector<int>& sizes)
+    {
+        reset(sizes);
+    }
+
+    template<typename T>
+    int Array<T>::getSize(const int index) const
+    {
+        if ((unsigned)index < mSize.size())
+            return mSize[index];
+        return 0;
+    }
+
+    template<typename T>
+    T& Array<T>::commonAt(const int index) const
+    {
+        if (index < 0 || (size_t)index >= mVolume)
+        {
+            std::fprintf(stderr, "oracle shim: Array index %d out of bounds (volume %zu)\n", index, mVolume);
+            std::abort();
+        }
+        return pData[index];
+    }
+
+#define OPREF_INSTANTIATE_ARRAY(T) \
+    template Array<T>::Array(const std::vector<int>&); \
+    template void Array<T>::reset(const int); \
+    template void Array<T>::reset(const std::vector<int>&); \
+    template void Array<T>::reset(const std::vector<int>&, const T); \
+    template int Array<T>::getSize(const int) const; \
+    template T& Array<T>::commonAt(const int) const
+    OPREF_INSTANTIATE_ARRAY(float);
+    OPREF_INSTANTIATE_ARRAY(double);
+
+    // (3)
+    template <typename T>
+    float getKeypointsRoi(const Rectangle<T>&, const Rectangle<T>&)
+    {
+        std::fprintf(stderr, "oracle shim: getKeypointsRoi reached (>=135-part model) - out of scope\n");
+        std::abort();
+    }
+    template float getKeypointsRoi(const Rectangle<float>&, const Rectangle<float>&);
+    template float getKeypointsRoi(const Rectangle<double>&, const Rectangle<double>&);
+}
+
+// (4) C entry surface -------------------------------------------------------------------------
+static thread_local char gErr[1024];
+
+extern "C"
+{
+    const char* ref_last_error() { return gErr; }
+
+    // nmsCpu, src/openpose/net/nmsBase.cpp:110-170
+    int ref_nms_cpu(float* target, int* kernel, const float* source, float threshold,
+                    const int* targetSize, const int* sourceSize, float offX, float offY)
+    {
+        try
+        {
+            const std::array<int, 4> t{{targetSize[0], targetSize[1], targetSize[2], targetSize[3]}};
+            const std::array<int, 4> s{{sourceSize[0], sourceSize[1], sourceSize[2], sourceSize[3]}};
+            op::nmsCpu(target, kernel, source, threshold, t, s, op::Point<float>{offX, offY});
+            return 0;
+        }
+        catch (const std::exception& e)
+        {
+            std::snprintf(gErr, sizeof(gErr), "%s", e.what());
+            return 1;
+        }
+    }
+
+    static int copyOut(const op::Array<float>& kp, const op::Array<float>& sc, float* outKeypoints,
+                       float* outScores, int capacityPeople, int parts)
+    {
+        const int people = kp.getSize(0);
+        const int n = people < capacityPeople ? people : capacityPeople;
+        if (n > 0)
+        {
+            std::memcpy(outKeypoints, kp.getConstPtr(), sizeof(float) * (size_t)n * parts * 3);
+            std::memcpy(outScores, sc.getConstPtr(), sizeof(float) * (size_t)n);
+        }
+        return people;
+    }
+
+    // connectBodyPartsCpu, src/openpose/net/bodyPartConnectorBase.cpp:1328-1377. Returns #people (or -1).
+    int ref_connect_cpu(const float* heatMap, const float* peaks, int poseModel, int width, int height,
+                        int maxPeaks, float interMinAboveThreshold, float interThreshold, int minSubsetCnt,
+                        float minSubsetScore, float defaultNmsThreshold, float scaleFactor,
+                        int maximizePositives, float* outKeypoints, float* outScores, int capacityPeople)
+    {
+        try
+        {
+            op::Array<float> kp, sc;
+            const auto model = (op::PoseModel)poseModel;
+            op::connectBodyPartsCpu(kp, sc, heatMap, peaks, model, op::Point<int>{width, height}, maxPeaks,
+                                    interMinAboveThreshold, interThreshold, minSubsetCnt, minSubsetScore,
+                                    defaultNmsThreshold, scaleFactor, maximizePositives != 0);
+            return copyOut(kp, sc, outKeypoints, outScores, capacityPeople, (int)op::getPoseNumberBodyParts(model));
+        }
+        catch (const std::exception& e)
+        {
+            std::snprintf(gErr, sizeof(gErr), "%s", e.what());
+            return -1;
+        }
+    }
+
+    // Host half of connectBodyPartsGpu (bodyPartConnectorBase.cu:209-230): pafPtrIntoVector ->
+    // pafVectorIntoPeopleVector -> removePeopleBelowThresholdsAndFillFaces -> peopleVectorToPeopleArray,
+    // fed with a (pairs, maxPeaks, maxPeaks) score cube.
+    int ref_connect_from_pair_scores(const float* pairScores, const float* peaks, int poseModel, int maxPeaks,
+                                     int minSubsetCnt, float minSubsetScore, float scaleFactor,
+                                     int maximizePositives, float* outKeypoints, float* outScores,
+                                     int capacityPeople)
+    {
+        try
+        {
+            const auto model = (op::PoseModel)poseModel;
+            const auto& pairs = op::getPosePartPairs(model);
+            const auto parts = op::getPoseNumberBodyParts(model);
+            const auto numberPairs = (unsigned int)(pairs.size() / 2);
+            op::Array<float> cube({(int)numberPairs, maxPeaks, maxPeaks});
+            std::memcpy(cube.getPtr(), pairScores, sizeof(float) * cube.getVolume());
+            const auto connections = op::pafPtrIntoVector(cube, peaks, maxPeaks, pairs, numberPairs);
+            auto people = op::pafVectorIntoPeopleVector(connections, peaks, maxPeaks, pairs, parts);
+            int numberPeople = 0;
+            std::vector<int> valid;
+            op::removePeopleBelowThresholdsAndFillFaces(valid, numberPeople, people, parts, minSubsetCnt,
+                                                        minSubsetScore, maximizePositives != 0, peaks);
+            op::Array<float> kp, sc;
+            op::peopleVectorToPeopleArray(kp, sc, scaleFactor, people, valid, peaks, numberPeople, parts,
+                                          numberPairs);
+            return copyOut(kp, sc, outKeypoints, outScores, capacityPeople, (int)parts);
+        }
+        catch (const std::exception& e)
+        {
+            std::snprintf(gErr, sizeof(gErr), "%s", e.what());
+            return -1;
+        }
+    }
+
+    // Model tables, src/openpose/pose/poseParameters.cpp:253-367,416-537
+    int ref_pose_number_body_parts(int poseModel) { return (int)op::getPoseNumberBodyParts((op::PoseModel)poseModel); }
+    int ref_pose_add_bkg(int poseModel) { return op::addBkgChannel((op::PoseModel)poseModel) ? 1 : 0; }
+    int ref_pose_max_peaks() { return (int)op::getPoseMaxPeaks(); }
+    int ref_pose_part_pairs(int poseModel, unsigned int* out, int capacity)
+    {
+        const auto& v = op::getPosePartPairs((op::PoseModel)poseModel);
+        for (size_t i = 0; i < v.size() && (int)i < capacity; i++)
+            out[i] = v[i];
+        return (int)v.size();
+    }
+    int ref_pose_map_index(int poseModel, unsigned int* out, int capacity)
+    {
+        const auto& v = op::getPoseMapIndex((op::PoseModel)poseModel);
+        for (size_t i = 0; i < v.size() && (int)i < capacity; i++)
+            out[i] = v[i];
+        return (int)v.size();
+    }
+    // out = {nmsThreshold, interMinAbove, interThreshold, minSubsetCnt, minSubsetScore}
+    void ref_pose_defaults(int poseModel, int maximizePositives, float* out)
+    {
+        const auto model = (op::PoseModel)poseModel;
+        const bool mp = maximizePositives != 0;
+        out[0] = op::getPoseDefaultNmsThreshold(model, mp);
+        out[1] = op::getPoseDefaultConnectInterMinAboveThreshold(mp);
+        out[2] = op::getPoseDefaultConnectInterThreshold(model, mp);
+        out[3] = (float)op::getPoseDefaultMinSubsetCnt(mp);
+        out[4] = op::getPoseDefaultConnectMinSubsetScore(mp);
+    }
+}
