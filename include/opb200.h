@@ -1,0 +1,119 @@
+/* opb200.h -- C ABI of the B200-native OpenPose hot path (libopb200.so).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types, no exceptions. Every entry
+ * point returns 0 on success or a non-zero opb200_status; opb200_last_error() then holds a message that
+ * the C++ shim (openpose_b200/csrc/op/) turns into op::error(...) exactly like the reference's
+ * try/catch -> error(e.what(), __LINE__, __FUNCTION__, __FILE__) convention
+ * (reference: src/openpose/utilities/errorAndLog.cpp:158-233).
+ *
+ * "reference" paths below are relative to the zengjianping/openpose tree.
+ * All data pointers are DEVICE pointers unless the name says host; `stream` is a cudaStream_t passed as
+ * void* (NULL = legacy default stream). Nothing in here synchronises the device unless stated.
+ */
+#ifndef OPB200_H
+#define OPB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int opb200_status;
+#define OPB200_OK 0
+#define OPB200_ERR_INVALID 1   /* bad argument (shape, threshold, too many scales ...) */
+#define OPB200_ERR_CUDA 2      /* a CUDA runtime call or kernel launch failed */
+#define OPB200_ERR_UNSUPPORTED 3
+#define OPB200_ERR_IO 4        /* prototxt / caffemodel missing or malformed */
+
+/* op::PoseModel values (reference: include/openpose/pose/enumClasses.hpp:9-30). */
+#define OPB200_POSE_BODY_25 0
+#define OPB200_POSE_COCO_18 1
+
+/* Which of the reference's two divergent semantics to reproduce. */
+#define OPB200_SEMANTICS_CPU 0  /* CPU_ONLY build: nmsBase.cpp, bodyPartConnectorBase.cpp createPeopleVector  */
+#define OPB200_SEMANTICS_CUDA 1 /* CUDA build: nmsBase.cu borders, process() scores, pafVectorIntoPeopleVector */
+
+#define OPB200_MAX_SCALES 8     /* reference: src/openpose/net/resizeAndMergeBase.cu:457-459 */
+
+const char* opb200_last_error(void);   /* thread-local, valid until the next failing call on this thread */
+int opb200_version(void);              /* ABI version, currently 1 */
+int opb200_device_count(void);         /* replaces op::getCudaGpuNumber, reference: src/openpose/gpu/cuda.cpp:41-61 */
+
+/* ---------------------------------------------------------------------------------------------------
+ * resizeAndMerge -- replaces op::resizeAndMergeGpu<float>
+ * (reference: include/openpose/net/resizeAndMergeBase.hpp:14-17, src/openpose/net/resizeAndMergeBase.cu:275-528).
+ * dst (dst_shape = N,C,H,W) = average over scales of the bicubic (Catmull-Rom, cuda.hu:91-144) upsampling of
+ * srcs[i] (src_shapes[i] = N_i,C,h_i,w_i). One scale: ratio 1 copies, otherwise the x/y ratios must be equal
+ * integers (the reference only implements x8; any integer factor is accepted here). Several scales (<= 8):
+ * per-scale factors derived from scale_ratios[i] (scaleInputToNetInputs) as resizeAndMergeBase.cu:379-380,475-477.
+ * N: every frame n of dst is built from frame n of each source (the reference merges only N == 1).
+ * `srcs` is a HOST array of device pointers.
+ * ------------------------------------------------------------------------------------------------- */
+opb200_status opb200_resize_merge(float* dst, const float* const* srcs, const int (*src_shapes)[4],
+                                  const float* scale_ratios, int n_scales, const int dst_shape[4],
+                                  void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * nms -- replaces op::nmsGpu<float> / op::nmsCpu<float>
+ * (reference: include/openpose/net/nmsBase.hpp:8-17, src/openpose/net/nmsBase.cpp:110-170, nmsBase.cu:249-351).
+ * heat (heat_shape = N,Ch,H,W): only channels [0, peaks_shape[1]) of each frame are scanned.
+ * peaks (peaks_shape = N,parts,maxPeaks+1,3): row 0 col 0 = count, rows 1..count = (x, y, score); rows beyond
+ * the count are left untouched, as in the reference.
+ * scratch: device buffer of at least opb200_nms_scratch_bytes(...) bytes (the reference's int "kernel" blob,
+ * nmsCaffe.cpp:123, is always large enough). mode = OPB200_SEMANTICS_*.
+ * ------------------------------------------------------------------------------------------------- */
+size_t opb200_nms_scratch_bytes(const int peaks_shape[4], const int heat_shape[4]);
+opb200_status opb200_nms(float* peaks, void* scratch, const float* heat, float threshold, float offset_x,
+                         float offset_y, const int peaks_shape[4], const int heat_shape[4], int mode,
+                         void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * maximum -- replaces op::maximumGpu<float> / op::maximumCpu<float>
+ * (reference: include/openpose/net/maximumBase.hpp, src/openpose/net/maximumBase.cpp:8-57, maximumBase.cu:63-120).
+ * source (N,C,H,W) -> target (N,1,C-1,3) = (x, y, value) of the first maximum in raster order of channels
+ * 0..C-2 (the background channel is skipped). scratch: >= opb200_maximum_scratch_bytes(...) bytes.
+ * ------------------------------------------------------------------------------------------------- */
+size_t opb200_maximum_scratch_bytes(const int target_shape[4], const int source_shape[4]);
+opb200_status opb200_maximum(float* target, void* scratch, const float* source, const int target_shape[4],
+                             const int source_shape[4], void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * bodyPartConnector -- replaces op::connectBodyPartsGpu<float> / op::connectBodyPartsCpu<float>
+ * (reference: include/openpose/net/bodyPartConnectorBase.hpp:8-24, src/openpose/net/bodyPartConnectorBase.cpp:
+ * 12-75 getScoreAB, 157-472 createPeopleVector, 721-884 filter, 887-934 output; .cu:15-66,108-145 scores).
+ * Everything (PAF line integrals, per-limb sort + greedy matching, person assembly, filtering, output) runs
+ * on the device; the host only reads the final arrays.
+ *   heat   (N,Ch,H,W) device: full heat-map blob (PAF channels at parts+1+mapIdx)
+ *   peaks  (N,parts,max_peaks+1,3) device: output of opb200_nms
+ *   out_keypoints (N,capacity,parts,3), out_scores (N,capacity), out_count (N) int32: device
+ * out_count[n] = number of people found (may exceed capacity; only the first `capacity` are written).
+ * ------------------------------------------------------------------------------------------------- */
+typedef struct opb200_connect_params
+{
+    int pose_model;               /* OPB200_POSE_* */
+    int max_peaks;                /* POSE_MAX_PEOPLE = 127 */
+    float inter_min_above_threshold;
+    float inter_threshold;
+    int min_subset_cnt;
+    float min_subset_score;
+    float default_nms_threshold;
+    float scale_factor;           /* scaleNetToOutput */
+    int maximize_positives;
+    int semantics;                /* OPB200_SEMANTICS_* */
+} opb200_connect_params;
+
+size_t opb200_connect_scratch_bytes(const opb200_connect_params* p, int n_frames);
+opb200_status opb200_connect(float* out_keypoints, float* out_scores, int* out_count, int capacity,
+                             void* scratch, const float* heat, const float* peaks, const int heat_shape[4],
+                             const opb200_connect_params* p, void* stream);
+/* Score cube only (pairs, max_peaks, max_peaks) per frame, as pafScoreKernel writes it
+ * (reference: src/openpose/net/bodyPartConnectorBase.cu:108-145); for tests and the CUDA-semantics path. */
+opb200_status opb200_paf_scores(float* cube, const float* heat, const float* peaks, const int heat_shape[4],
+                                const opb200_connect_params* p, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OPB200_H */

@@ -1,0 +1,327 @@
+// resizeAndMerge: bicubic (Catmull-Rom) upsampling of the net output to net-input resolution, averaged
+// over scales. Replaces op::resizeAndMergeGpu (reference: src/openpose/net/resizeAndMergeBase.cu:106-196,
+// 275-528; interpolation math include/openpose_private/gpu/cuda.hu:91-144).
+//
+// The reference evaluates the full 2-D bicubic (5 cubic polynomials, 16 taps) for every output pixel. The
+// polynomial is separable, so here each block first interpolates the few source rows it needs along x into
+// shared memory (x-pass), then every output pixel costs ONE 1-D cubic along y (y-pass). In the x8 kernel
+// the y-pass additionally hoists the tap-only sub-expressions A, B, C of
+//     A*d*d*d + B*d*d - C*d + v1            (cuda.hu:117-120, evaluated left to right)
+// out of the 8 output rows that share the same four taps, leaving 9 FP32 operations per output pixel, so
+// the kernel is bound by the 4*C*H*W output write (HBM roofline), not by FP32 issue.
+// All arithmetic keeps the reference's operation order with contraction disabled, i.e. it is bit-identical
+// to the non-fused evaluation of cuda.hu (the oracle, oracle/post_oracle.c:opo_resize_merge).
+#include "../common.cuh"
+
+namespace opb
+{
+    // cuda.hu:117-120, exact order, no FMA.
+    __device__ __forceinline__ float cubicA(float v0, float v1, float v2, float v3)
+    {
+        return add(sub(add(mul(-0.5f, v0), mul(1.5f, v1)), mul(1.5f, v2)), mul(0.5f, v3));
+    }
+    __device__ __forceinline__ float cubicB(float v0, float v1, float v2, float v3)
+    {
+        return sub(add(sub(v0, mul(2.5f, v1)), mul(2.f, v2)), mul(0.5f, v3));
+    }
+    __device__ __forceinline__ float cubicC(float v0, float v2) { return mul(0.5f, sub(v0, v2)); }
+    __device__ __forceinline__ float cubicEval(float A, float B, float C, float v1, float d)
+    {
+        const float t1 = mul(mul(mul(A, d), d), d);
+        const float t2 = mul(mul(B, d), d);
+        const float t3 = mul(C, d);
+        return add(sub(add(t1, t2), t3), v1);
+    }
+    __device__ __forceinline__ float cubic1d(float v0, float v1, float v2, float v3, float d)
+    {
+        return cubicEval(cubicA(v0, v1, v2, v3), cubicB(v0, v1, v2, v3), cubicC(v0, v2), v1, d);
+    }
+
+    // cuda.hu:96-106 for one axis: clamped tap indices + (unclamped) fractional offset.
+    __device__ __forceinline__ void taps(int idx[4], float& d, float s, int size)
+    {
+        idx[1] = min(size - 1, max(0, (int)floorf(s)));
+        idx[0] = max(0, idx[1] - 1);
+        idx[2] = min(size - 1, idx[1] + 1);
+        idx[3] = min(size - 1, idx[2] + 1);
+        d = sub(s, (float)idx[1]);
+    }
+    __host__ __device__ inline int align4(int v) { return (v + 3) & ~3; }
+    __device__ __forceinline__ float srcCoord(int x, float scale) { return sub(divf(add((float)x, 0.5f), scale), 0.5f); }
+    // (x + 0.5) / 8 - 0.5: the division by a power of two is exact, so a multiply gives the identical float.
+    __device__ __forceinline__ float srcCoord8(int x) { return sub(mul(add((float)x, 0.5f), 0.125f), 0.5f); }
+
+    // ------------------------------------------------------------------------------------------------
+    // x8 single-scale kernel. Block = (plane, chunk of G y-groups); a y-group is the run of <= 8 output rows
+    // that share floor(ys) = g, g in [-1, hs-1]  (rows 8g+4 .. 8g+11).
+    // ------------------------------------------------------------------------------------------------
+    constexpr int kR8Threads = 192;
+
+    template <int G>
+    __global__ void __launch_bounds__(kR8Threads) resize8Kernel(float* __restrict__ dst, const float* __restrict__ src,
+                                                                int hs, int ws, int ht, int wt)
+    {
+        extern __shared__ float sm[];
+        constexpr int kRows = G + 3;
+        float* srcRows = sm;               // [kRows][ws]
+        float* tmp = sm + align4(kRows * ws); // [kRows][wt], wt % 4 == 0 -> 16-byte aligned rows
+
+        const size_t planeIdx = blockIdx.y;
+        const float* __restrict__ sp = src + planeIdx * hs * ws;
+        float* __restrict__ dp = dst + planeIdx * (size_t)ht * wt;
+        const int g0 = (int)blockIdx.x * G - 1;
+        const int rbase = max(0, g0 - 1);
+        const int rtop = min(hs - 1, max(g0 + G - 1, 0) + 2);
+        const int nrows = rtop - rbase + 1;
+
+        for (int i = threadIdx.x; i < nrows * ws; i += kR8Threads)
+            srcRows[i] = __ldg(sp + (size_t)rbase * ws + i);
+        __syncthreads();
+
+        // x-pass: tmp[j][x] = cubic along x of source row rbase+j
+        for (int i = threadIdx.x; i < nrows * wt; i += kR8Threads)
+        {
+            const int j = i / wt, x = i - j * wt;
+            int xi[4];
+            float dx;
+            taps(xi, dx, srcCoord8(x), ws);
+            const float* r = srcRows + j * ws;
+            tmp[j * wt + x] = cubic1d(r[xi[0]], r[xi[1]], r[xi[2]], r[xi[3]], dx);
+        }
+        __syncthreads();
+
+        // y-pass: 4 columns per thread, 128-bit stores
+        const int quads = wt >> 2;
+        for (int q = threadIdx.x; q < quads; q += kR8Threads)
+        {
+#pragma unroll
+            for (int gi = 0; gi < G; gi++)
+            {
+                const int g = g0 + gi;
+                if (g > hs - 1)
+                    break;
+                const int y1 = min(hs - 1, max(0, g));
+                const int y0 = max(0, y1 - 1), y2 = min(hs - 1, y1 + 1), y3 = min(hs - 1, y2 + 1);
+                const float4 t0 = *reinterpret_cast<const float4*>(tmp + (y0 - rbase) * wt + 4 * q);
+                const float4 t1 = *reinterpret_cast<const float4*>(tmp + (y1 - rbase) * wt + 4 * q);
+                const float4 t2 = *reinterpret_cast<const float4*>(tmp + (y2 - rbase) * wt + 4 * q);
+                const float4 t3 = *reinterpret_cast<const float4*>(tmp + (y3 - rbase) * wt + 4 * q);
+                const float Ax = cubicA(t0.x, t1.x, t2.x, t3.x), Bx = cubicB(t0.x, t1.x, t2.x, t3.x), Cx = cubicC(t0.x, t2.x);
+                const float Ay = cubicA(t0.y, t1.y, t2.y, t3.y), By = cubicB(t0.y, t1.y, t2.y, t3.y), Cy = cubicC(t0.y, t2.y);
+                const float Az = cubicA(t0.z, t1.z, t2.z, t3.z), Bz = cubicB(t0.z, t1.z, t2.z, t3.z), Cz = cubicC(t0.z, t2.z);
+                const float Aw = cubicA(t0.w, t1.w, t2.w, t3.w), Bw = cubicB(t0.w, t1.w, t2.w, t3.w), Cw = cubicC(t0.w, t2.w);
+                const int yBegin = max(0, 8 * g + 4), yEnd = min(ht, 8 * g + 12);
+                for (int y = yBegin; y < yEnd; y++)
+                {
+                    const float dy = sub(srcCoord8(y), (float)y1);
+                    float4 o;
+                    o.x = cubicEval(Ax, Bx, Cx, t1.x, dy);
+                    o.y = cubicEval(Ay, By, Cy, t1.y, dy);
+                    o.z = cubicEval(Az, Bz, Cz, t1.z, dy);
+                    o.w = cubicEval(Aw, Bw, Cw, t1.w, dy);
+                    *reinterpret_cast<float4*>(dp + (size_t)y * wt + 4 * q) = o;
+                }
+            }
+        }
+    }
+
+    // ------------------------------------------------------------------------------------------------
+    // Generic kernel: any number of scales (<= 8), any per-scale factors. Block = (plane, band of kBandRows
+    // output rows). Per scale: x-pass of the needed source rows into shared memory, then a 1-D cubic per pixel.
+    // ------------------------------------------------------------------------------------------------
+    constexpr int kGenThreads = 256;
+    constexpr int kBandRows = 8;
+    constexpr int kMaxTmpRows = 14;
+
+    struct MergeArgs
+    {
+        const float* src[OPB200_MAX_SCALES];
+        int hs[OPB200_MAX_SCALES], ws[OPB200_MAX_SCALES];
+        float scaleW[OPB200_MAX_SCALES], scaleH[OPB200_MAX_SCALES];
+        int nScales, ht, wt, maxTmpRows;
+    };
+
+    __global__ void __launch_bounds__(kGenThreads) resizeMergeKernel(float* __restrict__ dst, const MergeArgs a)
+    {
+        extern __shared__ float tmp[]; // [maxTmpRows][wt]
+        const size_t planeIdx = blockIdx.y;
+        const int yBand = blockIdx.x * kBandRows;
+        const int rowsHere = min(kBandRows, a.ht - yBand);
+        const int nPix = rowsHere * a.wt;
+        constexpr int kSlots = 24; // pixels per thread kept in registers
+        float acc[kSlots];
+#pragma unroll
+        for (int k = 0; k < kSlots; k++)
+            acc[k] = 0.f;
+
+        for (int pixBase = 0; pixBase < nPix; pixBase += kSlots * kGenThreads)
+        {
+#pragma unroll
+            for (int k = 0; k < kSlots; k++)
+                acc[k] = 0.f;
+            for (int i = 0; i < a.nScales; i++)
+            {
+                const float* __restrict__ sp = a.src[i] + planeIdx * a.hs[i] * a.ws[i];
+                int yi[4];
+                float dyDummy;
+                taps(yi, dyDummy, srcCoord(yBand, a.scaleH[i]), a.hs[i]);
+                const int rlo = yi[0];
+                taps(yi, dyDummy, srcCoord(yBand + rowsHere - 1, a.scaleH[i]), a.hs[i]);
+                const int rhi = yi[3];
+                const int nrows = rhi - rlo + 1;
+                const bool staged = nrows <= a.maxTmpRows; // block-uniform
+                if (staged)
+                {
+                    __syncthreads();
+                    for (int t = threadIdx.x; t < nrows * a.wt; t += kGenThreads)
+                    {
+                        const int j = t / a.wt, x = t - j * a.wt;
+                        int xi[4];
+                        float dx;
+                        taps(xi, dx, srcCoord(x, a.scaleW[i]), a.ws[i]);
+                        const float* r = sp + (size_t)(rlo + j) * a.ws[i];
+                        tmp[t] = cubic1d(__ldg(r + xi[0]), __ldg(r + xi[1]), __ldg(r + xi[2]), __ldg(r + xi[3]), dx);
+                    }
+                    __syncthreads();
+                }
+#pragma unroll
+                for (int k = 0; k < kSlots; k++)
+                {
+                    const int p = pixBase + k * kGenThreads + threadIdx.x;
+                    if (p < nPix)
+                    {
+                        const int yy = p / a.wt, x = p - yy * a.wt;
+                        float dy;
+                        taps(yi, dy, srcCoord(yBand + yy, a.scaleH[i]), a.hs[i]);
+                        float t4[4];
+                        if (staged)
+                        {
+#pragma unroll
+                            for (int r = 0; r < 4; r++)
+                                t4[r] = tmp[(yi[r] - rlo) * a.wt + x];
+                        }
+                        else
+                        {
+                            int xi[4];
+                            float dx;
+                            taps(xi, dx, srcCoord(x, a.scaleW[i]), a.ws[i]);
+#pragma unroll
+                            for (int r = 0; r < 4; r++)
+                            {
+                                const float* rr = sp + (size_t)yi[r] * a.ws[i];
+                                t4[r] = cubic1d(__ldg(rr + xi[0]), __ldg(rr + xi[1]), __ldg(rr + xi[2]), __ldg(rr + xi[3]), dx);
+                            }
+                        }
+                        acc[k] = add(acc[k], cubic1d(t4[0], t4[1], t4[2], t4[3], dy));
+                    }
+                }
+            }
+            float* __restrict__ dp = dst + planeIdx * (size_t)a.ht * a.wt + (size_t)yBand * a.wt;
+            const float cnt = (float)a.nScales;
+#pragma unroll
+            for (int k = 0; k < kSlots; k++)
+            {
+                const int p = pixBase + k * kGenThreads + threadIdx.x;
+                if (p < nPix)
+                    dp[p] = a.nScales == 1 ? acc[k] : divf(acc[k], cnt);
+            }
+        }
+    }
+
+    template <int G>
+    static cudaError_t launch8(float* dst, const float* src, int planes, int hs, int ws, int ht, int wt, cudaStream_t st)
+    {
+        const size_t smem = sizeof(float) * ((size_t)align4((G + 3) * ws) + (size_t)(G + 3) * wt);
+        cudaError_t e = cudaFuncSetAttribute(resize8Kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess)
+            return e;
+        const dim3 grid((hs + 1 + G - 1) / G, planes);
+        resize8Kernel<G><<<grid, kR8Threads, smem, st>>>(dst, src, hs, ws, ht, wt);
+        return cudaPeekAtLastError();
+    }
+}
+
+extern "C" opb200_status opb200_resize_merge(float* dst, const float* const* srcs, const int (*src_shapes)[4],
+                                             const float* scale_ratios, int n_scales, const int dst_shape[4],
+                                             void* stream)
+{
+    using namespace opb;
+    OPB_REQUIRE(dst && srcs && src_shapes && dst_shape, "resizeAndMerge: null argument");
+    // reference: resizeAndMergeBase.cu:282-288, 457-459
+    OPB_REQUIRE(n_scales >= 1, "sourceSizes cannot be empty.");
+    OPB_REQUIRE(n_scales <= OPB200_MAX_SCALES, "More than 8 scales are not implemented (yet). Notify us to implement it.");
+    const int n = dst_shape[0], c = dst_shape[1], ht = dst_shape[2], wt = dst_shape[3];
+    OPB_REQUIRE(n > 0 && c > 0 && ht > 0 && wt > 0, "resizeAndMerge: empty target");
+    for (int i = 0; i < n_scales; i++)
+    {
+        OPB_REQUIRE(srcs[i] != nullptr, "resizeAndMerge: null source");
+        OPB_REQUIRE(src_shapes[i][0] == n && src_shapes[i][1] == c && src_shapes[i][2] > 0 && src_shapes[i][3] > 0,
+                    "resizeAndMerge: source shape inconsistent with target (N, C must match)");
+    }
+    const long long planes = (long long)n * c;
+    OPB_REQUIRE(planes <= 65535, "resizeAndMerge: too many planes for one launch");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int hs = src_shapes[0][2], ws = src_shapes[0][3];
+
+    MergeArgs a;
+    a.nScales = n_scales;
+    a.ht = ht;
+    a.wt = wt;
+    if (n_scales == 1)
+    {
+        if (wt / ws == 1 && ht / hs == 1)
+        {
+            // reference: fillKernel, resizeAndMergeBase.cu:342-349
+            OPB_REQUIRE(wt == ws && ht == hs, "resizeAndMerge: ratio-1 copy needs identical sizes");
+            OPB_CUDA(cudaMemcpyAsync(dst, srcs[0], sizeof(float) * planes * ht * wt, cudaMemcpyDeviceToDevice, st));
+            return OPB200_OK;
+        }
+        OPB_REQUIRE(wt / ws == 8 && ht / hs == 8,
+                    "Kernel only implemented for 8x resize. Notify us if this error appears.");
+        const bool aligned = ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0) && (wt % 4 == 0);
+        if (wt == 8 * ws && ht == 8 * hs && aligned)
+        {
+            const long long blocks4 = planes * ((hs + 1 + 3) / 4);
+            cudaError_t e;
+            if (blocks4 >= 2ll * kNumSMsB200 * 8)
+                e = launch8<4>(dst, srcs[0], (int)planes, hs, ws, ht, wt, st);
+            else if (blocks4 >= 1ll * kNumSMsB200 * 4)
+                e = launch8<2>(dst, srcs[0], (int)planes, hs, ws, ht, wt, st);
+            else
+                e = launch8<1>(dst, srcs[0], (int)planes, hs, ws, ht, wt, st);
+            OPB_CUDA(e);
+            return OPB200_OK;
+        }
+        a.scaleW[0] = 8.f;
+        a.scaleH[0] = 8.f;
+    }
+    else
+    {
+        // reference: resizeAndMergeBase.cu:379-380, 475-477 (all FP32)
+        OPB_REQUIRE(scale_ratios != nullptr, "resizeAndMerge: scale ratios required for multi-scale merging");
+        const float mainW = wt / (float)ws;
+        const float mainH = ht / (float)hs;
+        for (int i = 0; i < n_scales; i++)
+        {
+            const float r = scale_ratios[i] / scale_ratios[0];
+            a.scaleW[i] = mainW / r;
+            a.scaleH[i] = mainH / r;
+        }
+    }
+    for (int i = 0; i < n_scales; i++)
+    {
+        a.src[i] = srcs[i];
+        a.hs[i] = src_shapes[i][2];
+        a.ws[i] = src_shapes[i][3];
+    }
+    const size_t rowBytes = sizeof(float) * (size_t)wt;
+    int rows = (int)((200u * 1024u) / rowBytes);
+    rows = rows > kMaxTmpRows ? kMaxTmpRows : rows;
+    a.maxTmpRows = rows >= 4 ? rows : 0;
+    const size_t smem = rowBytes * (size_t)a.maxTmpRows;
+    OPB_CUDA(cudaFuncSetAttribute(resizeMergeKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem > 0 ? smem : 4)));
+    const dim3 grid((ht + kBandRows - 1) / kBandRows, (unsigned)planes);
+    resizeMergeKernel<<<grid, kGenThreads, smem, st>>>(dst, a);
+    OPB_LAUNCH_CHECK();
+    return OPB200_OK;
+}
