@@ -113,6 +113,47 @@ opb200_status opb200_connect(float* out_keypoints, float* out_scores, int* out_c
 opb200_status opb200_paf_scores(float* cube, const float* heat, const float* peaks, const int heat_shape[4],
                                 const opb200_connect_params* p, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * NetB200 -- replaces op::NetCaffe behind op::Net
+ * (reference: include/openpose/net/net.hpp:8-18, include/openpose/net/netCaffe.hpp:12-13,
+ *  src/openpose/net/netCaffe.cpp:45-99 constructor checks, :154-210 initializationOnThread,
+ *  :212-261 forwardPass, :263-278 getOutputBlobArray).
+ * opb200_net_create = constructor + initializationOnThread: checks both files exist (same messages), parses
+ * the prototxt and the caffemodel (weights matched by layer name), plans the graph and uploads bf16 weights
+ * to device gpu_id. last_blob_name NULL/"" = "net_output"; an unknown name fails with NetCaffe's message.
+ * opb200_net_forward = forwardPass: input (N,3,H,W) fp32 NCHW on the host (input_on_device = 0; copied
+ * inside the call, stream-ordered) or on the device; re-plans buffers when the shape changes; enqueues
+ * the forward pass stream-ordered after `stream` and makes `stream` wait for it (no host synchronisation).
+ * opb200_net_output = getOutputBlobArray: device pointer + shape of the fp32 NCHW output blob, owned by the
+ * net, valid until the next reshaping forward or destroy.
+ * Convolutions run in bf16 with fp32 accumulation on tcgen05 tensor cores; supported layer types:
+ * Convolution (stride 1, "same" odd kernels), ReLU, PReLU, MAX Pooling (no pad), Concat (axis 1), Input.
+ * ------------------------------------------------------------------------------------------------- */
+typedef struct opb200_net opb200_net;
+typedef struct opb200_net_info_t
+{
+    int conv_layers;
+    int kernel_launches_per_forward;
+    double flops_per_forward;     /* algorithmic conv FLOPs at the current shape: 2*Cout*Cin*k*k*H*W*N */
+    double arena_bytes;
+    int output_channels;
+} opb200_net_info_t;
+
+opb200_status opb200_net_create(opb200_net** out, const char* prototxt, const char* caffemodel, int gpu_id,
+                                const char* last_blob_name);
+void opb200_net_destroy(opb200_net* net);
+opb200_status opb200_net_forward(opb200_net* net, const float* input, int input_on_device, const int shape[4],
+                                 void* stream);
+opb200_status opb200_net_output(opb200_net* net, const float** dev_ptr, int shape[4]);
+opb200_status opb200_net_info(opb200_net* net, opb200_net_info_t* info);
+/* Test hook: any intermediate blob as fp32 NCHW on the host (host_nchw NULL = shape query). Synchronises. */
+opb200_status opb200_net_read_blob(opb200_net* net, const char* name, float* host_nchw, size_t capacity,
+                                   int shape[4]);
+
+/* Host-only (no CUDA call): parse + plan the model and write one text line per planned kernel launch. */
+opb200_status opb200_net_describe(const char* prototxt, const char* caffemodel, const char* last_blob_name,
+                                  char* text, size_t capacity);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,22 @@
+// Internal launch interface between the net runtime (net_runtime.cu) and its kernels.
+#pragma once
+#include "../common.cuh"
+#include "conv_params.h"
+
+namespace opb
+{
+    opb200_status launchConv(const ConvParams& p, int bn, int gridCap, cudaStream_t st);
+    opb200_status launchInputPatch(void* dstBf16Nhwc, const float* srcNchw, int N, int C, int H, int W, int k, int pad,
+                                   int dstC, cudaStream_t st);
+    opb200_status launchMaxPool(void* dst, const void* src, int N, int C, int H, int W, int Ho, int Wo, int k,
+                                int stride, int srcStride, int dstStride, cudaStream_t st);
+    opb200_status launchNhwcToNchw(float* dst, const void* src, int N, int C, int H, int W, int srcStride, int dstC,
+                                   int dstOff, cudaStream_t st);
+
+    // cuTensorMapEncodeTiled through cudaGetDriverEntryPoint (no link-time dependency on libcuda).
+    // Activation view: dims (C, W, H, N) of bf16, pixel stride `strideC` elements; box (boxC, TW, TH, 1).
+    opb200_status makeActivationMap(CUtensorMap* m, const void* base, int C, int W, int H, int N, int strideC,
+                                    int boxC, int TW, int TH, bool swizzle128);
+    // Weight matrix: dims (K, rows) of bf16 row-major; box (64, boxRows), SWIZZLE_128B.
+    opb200_status makeWeightMap(CUtensorMap* m, const void* base, int K, int rows, int boxRows);
+}

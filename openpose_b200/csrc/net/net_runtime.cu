@@ -1,0 +1,1059 @@
+// NetB200: the Caffe-free op::Net backend. Loads prototxt + caffemodel, plans the graph once (conv + bias +
+// activation fused, concat by channel offset / multi-segment reads, weights repacked to bf16 K-major), and runs
+// the forward pass as a stream of hand-written sm_100a kernels (conv_sm100.cu, aux_kernels.cu).
+//
+// Replaces op::NetCaffe (reference: src/openpose/net/netCaffe.cpp:45-99 ctor checks, :154-210 initialization,
+// :212-261 forwardPass, :263-278 getOutputBlobArray) and the Caffe inference subset underneath it
+// (3rdparty/caffe/src/caffe/net.cpp:518-535 ForwardFromTo; conv/relu/prelu/pooling/concat layers).
+// Exposed through the C ABI declared in include/opb200.h (opb200_net_*).
+#include "caffe_format.h"
+#include "net_kernels.h"
+#include <cuda_bf16.h>
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <set>
+#include <string>
+#include <vector>
+
+namespace opb
+{
+    // ------------------------------------------------------------------------------------------------
+    // tensor maps
+    // ------------------------------------------------------------------------------------------------
+    typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                      const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                      CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+    static EncodeTiledFn encodeTiled()
+    {
+        static EncodeTiledFn fn = nullptr;
+        if (!fn)
+        {
+            void* p = nullptr;
+            cudaDriverEntryPointQueryResult q;
+            if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+                q == cudaDriverEntryPointSuccess)
+                fn = reinterpret_cast<EncodeTiledFn>(p);
+        }
+        return fn;
+    }
+
+    opb200_status makeActivationMap(CUtensorMap* m, const void* base, int C, int W, int H, int N, int strideC,
+                                    int boxC, int TW, int TH, bool swizzle128)
+    {
+        EncodeTiledFn fn = encodeTiled();
+        if (!fn)
+            OPB_FAIL(OPB200_ERR_CUDA, "cuTensorMapEncodeTiled is unavailable (driver too old?)");
+        const cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+        const cuuint64_t strides[3] = {(cuuint64_t)strideC * 2, (cuuint64_t)strideC * 2 * W,
+                                       (cuuint64_t)strideC * 2 * W * H};
+        const cuuint32_t box[4] = {(cuuint32_t)boxC, (cuuint32_t)TW, (cuuint32_t)TH, 1};
+        const cuuint32_t es[4] = {1, 1, 1, 1};
+        const CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, es,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS)
+        {
+            setError("cuTensorMapEncodeTiled(activation C=%d W=%d H=%d N=%d stride=%d box=%d,%d,%d) failed: %d", C, W,
+                     H, N, strideC, boxC, TW, TH, (int)r);
+            return OPB200_ERR_CUDA;
+        }
+        return OPB200_OK;
+    }
+
+    opb200_status makeWeightMap(CUtensorMap* m, const void* base, int K, int rows, int boxRows)
+    {
+        EncodeTiledFn fn = encodeTiled();
+        if (!fn)
+            OPB_FAIL(OPB200_ERR_CUDA, "cuTensorMapEncodeTiled is unavailable (driver too old?)");
+        const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+        const cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+        const cuuint32_t box[2] = {64, (cuuint32_t)boxRows};
+        const cuuint32_t es[2] = {1, 1};
+        const CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, es,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS)
+        {
+            setError("cuTensorMapEncodeTiled(weights K=%d rows=%d box=%d) failed: %d", K, rows, boxRows, (int)r);
+            return OPB200_ERR_CUDA;
+        }
+        return OPB200_OK;
+    }
+
+    // ------------------------------------------------------------------------------------------------
+    // plan
+    // ------------------------------------------------------------------------------------------------
+    struct View   // a channel range of a device buffer (bf16 NHWC)
+    {
+        int buf = -1, cOff = 0, C = 0;
+    };
+    struct Blob
+    {
+        int C = 0, level = 0;
+        bool isInput = false;
+        std::vector<View> segs;   // >1: virtual concat (read as several TMA segments)
+    };
+    struct Buffer
+    {
+        int C = 0, level = 0;     // allocated channels (multiple of 8)
+        size_t offset = 0;        // into the arena, set by reshape
+    };
+    enum OpKind
+    {
+        OP_PATCH,
+        OP_CONV,
+        OP_POOL,
+        OP_CONVERT
+    };
+    struct Op
+    {
+        OpKind kind = OP_CONV;
+        std::string name;
+        int level = 0, outLevel = 0;
+        std::vector<View> in;
+        View out;
+        // conv
+        int cin = 0, cout = 0, k = 1, pad = 0, bn = 128, nTilesN = 1, chunksTotal = 0, kTotal = 0;
+        int segChunks[kConvMaxSegments] = {0, 0, 0, 0};
+        std::vector<__nv_bfloat16> hostW;   // [nTilesN*bn][kTotal]
+        std::vector<float> hostBias, hostSlope;
+        __nv_bfloat16* dW = nullptr;
+        float *dBias = nullptr, *dSlope = nullptr;
+        int out32Off = -1;
+        bool storeBf16 = true;
+        double flopsPerPixel = 0;   // algorithmic: 2 * cout * cin * k * k
+        // pool
+        int stride = 1;
+        // patch (first layer im2col): k, pad reuse the fields above; inC = network input channels
+        int inC = 0;
+        ConvParams cp;
+    };
+
+    struct Level
+    {
+        int parent = -1, k = 1, stride = 1, pad = 0;   // level 0 = network input resolution
+    };
+
+    struct Net
+    {
+        int gpu = 0;
+        std::string lastBlobName;
+        NetDef def;
+        std::map<std::string, int> blobIndex;
+        std::vector<Blob> blobs;
+        std::vector<Buffer> buffers;
+        std::vector<Level> levels;
+        std::vector<Op> ops;
+        int inputC = 3;
+        int outBlob = -1, outC = 0, outLevel = 0;
+        // shape-dependent state
+        int N = 0, H = 0, W = 0;
+        std::vector<int> lvH, lvW;
+        uint8_t* arena = nullptr;
+        size_t arenaBytes = 0;
+        float* dInput = nullptr;
+        float* dOut32 = nullptr;
+        size_t inputBytes = 0, outBytes = 0;
+        cudaGraphExec_t graphExec = nullptr;
+        const float* graphInput = nullptr;
+        cudaStream_t graphStream = nullptr;
+        bool useGraph = true;
+        double flopsPerForward = 0;
+        int gridCap = kNumSMsB200;
+
+        ~Net()
+        {
+            if (graphExec)
+                cudaGraphExecDestroy(graphExec);
+            if (arena)
+                cudaFree(arena);
+            for (auto& o : ops)
+            {
+                if (o.dW)
+                    cudaFree(o.dW);
+                if (o.dBias)
+                    cudaFree(o.dBias);
+                if (o.dSlope)
+                    cudaFree(o.dSlope);
+            }
+        }
+    };
+
+    static int round8(int c) { return (c + 7) / 8 * 8; }
+
+    static int newBuffer(Net& net, int C, int level)
+    {
+        Buffer b;
+        b.C = round8(C);
+        b.level = level;
+        net.buffers.push_back(b);
+        return (int)net.buffers.size() - 1;
+    }
+
+    static bool overlaps(const View& a, const View& b)
+    {
+        return a.buf == b.buf && a.cOff < b.cOff + b.C && b.cOff < a.cOff + a.C;
+    }
+
+    static opb200_status planFail(const std::string& msg)
+    {
+        setError("%s", msg.c_str());
+        return OPB200_ERR_UNSUPPORTED;
+    }
+
+    static opb200_status planNet(Net& net, const WeightMap& wm)
+    {
+        const NetDef& def = net.def;
+        // ---- input blob ---------------------------------------------------------------------------
+        std::string inputName;
+        if (!def.inputs.empty())
+        {
+            inputName = def.inputs[0];
+            if (def.inputDim.size() >= 2)
+                net.inputC = def.inputDim[1];
+        }
+        for (const auto& L : def.layers)
+            if (L.type == "Input" && !L.tops.empty() && inputName.empty())
+            {
+                inputName = L.tops[0];
+                if (L.inputShape.size() >= 2)
+                    net.inputC = L.inputShape[1];
+            }
+        if (inputName.empty())
+            return planFail("prototxt: the net declares no input blob");
+        net.levels.push_back(Level());
+        {
+            Blob b;
+            b.C = net.inputC;
+            b.isInput = true;
+            net.blobIndex[inputName] = 0;
+            net.blobs.push_back(b);
+        }
+        // ---- pass 1: channel counts of every top, producer type ----------------------------------
+        std::map<std::string, int> chan;
+        std::map<std::string, std::string> producerType;
+        chan[inputName] = net.inputC;
+        producerType[inputName] = "Input";
+        for (const auto& L : def.layers)
+        {
+            if (L.type == "Input" || L.tops.empty())
+                continue;
+            int c = 0;
+            if (L.type == "Convolution")
+                c = L.numOutput;
+            else if (L.type == "Concat")
+            {
+                for (const auto& b : L.bottoms)
+                {
+                    if (!chan.count(b))
+                        return planFail("prototxt: layer " + L.name + " reads unknown blob " + b);
+                    c += chan[b];
+                }
+            }
+            else
+            {
+                if (L.bottoms.empty() || !chan.count(L.bottoms[0]))
+                    return planFail("prototxt: layer " + L.name + " reads an unknown blob");
+                c = chan[L.bottoms[0]];
+            }
+            chan[L.tops[0]] = c;
+            if (!(L.bottoms.size() == 1 && L.bottoms[0] == L.tops[0]))   // in-place layers keep the producer
+                producerType[L.tops[0]] = L.type;
+        }
+        // ---- pass 2: co-location claims: a concat whose members are all fresh conv/pool outputs gets one
+        //      buffer and its members are written straight into their channel slots ----------------------
+        struct Claim
+        {
+            std::string concat;
+            int off;
+        };
+        std::map<std::string, Claim> claims;
+        std::set<std::string> owningConcats;
+        for (const auto& L : def.layers)
+        {
+            if (L.type != "Concat")
+                continue;
+            bool ok = true;
+            int off = 0;
+            std::set<std::string> seen;
+            for (const auto& b : L.bottoms)
+            {
+                const std::string& pt = producerType[b];
+                if (claims.count(b) || seen.count(b) || (pt != "Convolution" && pt != "Pooling") || off % 8 != 0)
+                    ok = false;
+                seen.insert(b);
+                off += chan[b];
+            }
+            if (!ok)
+                continue;
+            off = 0;
+            for (const auto& b : L.bottoms)
+            {
+                claims[b] = Claim{L.tops[0], off};
+                off += chan[b];
+            }
+            owningConcats.insert(L.tops[0]);
+        }
+        std::map<std::string, int> concatBuffer;   // owning concat top -> buffer id (created on first use)
+        auto outputView = [&](const std::string& top, int C, int level) -> View {
+            View v;
+            v.C = C;
+            auto it = claims.find(top);
+            if (it == claims.end())
+            {
+                v.buf = newBuffer(net, C, level);
+                v.cOff = 0;
+                return v;
+            }
+            auto cb = concatBuffer.find(it->second.concat);
+            if (cb == concatBuffer.end())
+            {
+                const int id = newBuffer(net, chan[it->second.concat], level);
+                cb = concatBuffer.insert({it->second.concat, id}).first;
+            }
+            v.buf = cb->second;
+            v.cOff = it->second.off;
+            return v;
+        };
+
+        // ---- pass 3: ops ----------------------------------------------------------------------------
+        const bool bn256 = std::getenv("OPB200_CONV_BN256") != nullptr;
+        std::vector<bool> consumed(def.layers.size(), false);
+        for (size_t li = 0; li < def.layers.size(); ++li)
+        {
+            const LayerDef& L = def.layers[li];
+            if (consumed[li] || L.type == "Input")
+                continue;
+            if (L.tops.size() != 1)
+                return planFail("layer " + L.name + ": exactly one top is supported");
+            std::vector<const Blob*> ins;
+            for (const auto& b : L.bottoms)
+            {
+                auto it = net.blobIndex.find(b);
+                if (it == net.blobIndex.end())
+                    return planFail("layer " + L.name + " reads blob " + b + " before it is produced");
+                ins.push_back(&net.blobs[it->second]);
+            }
+            Blob top;
+            if (L.type == "Convolution")
+            {
+                if (ins.size() != 1)
+                    return planFail("layer " + L.name + ": convolution needs one bottom");
+                if (L.group != 1 || L.dilation != 1 || L.stride != 1 || L.kernel % 2 != 1 || L.pad != L.kernel / 2)
+                    return planFail("layer " + L.name +
+                                    ": only stride-1, group-1, undilated, odd-kernel 'same' convolutions are supported");
+                const Blob src = *ins[0];
+                auto w = wm.find(L.name);
+                if (w == wm.end() || w->second.empty())
+                    return planFail("caffemodel has no weights for layer " + L.name);
+                const int cin = src.C, cout = L.numOutput, k = L.kernel;
+                const BlobData& W = w->second[0];
+                if (W.data.size() != (size_t)cout * cin * k * k)
+                    return planFail("caffemodel: weight blob of layer " + L.name + " has the wrong size");
+                if (L.biasTerm && (w->second.size() < 2 || w->second[1].data.size() != (size_t)cout))
+                    return planFail("caffemodel: bias blob of layer " + L.name + " has the wrong size");
+                Op op;
+                op.kind = OP_CONV;
+                op.name = L.name;
+                op.level = op.outLevel = src.level;
+                op.cin = cin;
+                op.cout = cout;
+                op.flopsPerPixel = 2.0 * cout * cin * k * k;
+                bool patch = false;
+                if (src.isInput)
+                {
+                    // first layer: fp32 NCHW input -> bf16 patch tensor; conv becomes 1x1 when Cin*k*k <= 64
+                    patch = cin * k * k <= kConvBlockK;
+                    Op pre;
+                    pre.kind = OP_PATCH;
+                    pre.name = L.name + "/input";
+                    pre.level = pre.outLevel = src.level;
+                    pre.inC = cin;
+                    pre.k = patch ? k : 1;
+                    pre.pad = patch ? L.pad : 0;
+                    pre.out.C = patch ? cin * k * k : cin;
+                    pre.out.buf = newBuffer(net, pre.out.C, src.level);
+                    op.in.push_back(pre.out);
+                    net.ops.push_back(pre);
+                    op.k = patch ? 1 : k;
+                    op.pad = patch ? 0 : L.pad;
+                }
+                else
+                {
+                    op.in = src.segs;
+                    op.k = k;
+                    op.pad = L.pad;
+                }
+                if (op.in.size() > (size_t)kConvMaxSegments)
+                    return planFail("layer " + L.name + ": more than 4 concatenated inputs");
+                op.bn = cout <= 32 ? 32 : (cout <= 64 ? 64 : (cout <= 96 ? 96 : 128));
+                if (bn256 && cout % 256 == 0)
+                    op.bn = 256;
+                op.nTilesN = (cout + op.bn - 1) / op.bn;
+                op.chunksTotal = 0;
+                for (size_t s = 0; s < op.in.size(); ++s)
+                {
+                    op.segChunks[s] = (op.in[s].C + kConvBlockK - 1) / kConvBlockK;
+                    op.chunksTotal += op.segChunks[s];
+                }
+                const int taps = op.k * op.k;
+                op.kTotal = taps * op.chunksTotal * kConvBlockK;
+                const int rows = op.nTilesN * op.bn;
+                op.hostW.assign((size_t)rows * op.kTotal, __float2bfloat16(0.f));
+                op.hostBias.assign(rows, 0.f);
+                op.hostSlope.assign(rows, 1.f);   // identity unless an activation layer follows
+                if (patch)
+                {
+                    for (int co = 0; co < cout; ++co)
+                        for (int j = 0; j < cin * k * k; ++j)
+                            op.hostW[(size_t)co * op.kTotal + j] = __float2bfloat16(W.data[(size_t)co * cin * k * k + j]);
+                }
+                else
+                {
+                    int segStart = 0, chunkStart = 0;
+                    for (size_t s = 0; s < op.in.size(); ++s)
+                    {
+                        for (int c = 0; c < op.in[s].C; ++c)
+                        {
+                            const int ci = segStart + c;
+                            for (int t = 0; t < taps; ++t)
+                            {
+                                const size_t col = ((size_t)t * op.chunksTotal + chunkStart) * kConvBlockK + c;
+                                for (int co = 0; co < cout; ++co)
+                                    op.hostW[(size_t)co * op.kTotal + col] =
+                                        __float2bfloat16(W.data[((size_t)co * cin + ci) * taps + t]);
+                            }
+                        }
+                        segStart += op.in[s].C;
+                        chunkStart += op.segChunks[s];
+                    }
+                    if (segStart != cin)
+                        return planFail("layer " + L.name + ": input channel bookkeeping mismatch");
+                }
+                if (L.biasTerm)
+                    for (int co = 0; co < cout; ++co)
+                        op.hostBias[co] = w->second[1].data[co];
+                // fuse the in-place activation that follows (ReLU / PReLU)
+                for (size_t lj = li + 1; lj < def.layers.size(); ++lj)
+                {
+                    const LayerDef& A = def.layers[lj];
+                    const bool inPlace = A.bottoms.size() == 1 && A.tops.size() == 1 && A.bottoms[0] == L.tops[0] &&
+                                         A.tops[0] == L.tops[0];
+                    if (!inPlace)
+                    {
+                        bool reads = false;
+                        for (const auto& b : A.bottoms)
+                            reads = reads || b == L.tops[0];
+                        if (reads)
+                            break;      // a consumer: no activation in between
+                        continue;
+                    }
+                    if (A.type == "ReLU")
+                        std::fill(op.hostSlope.begin(), op.hostSlope.end(), 0.f);
+                    else if (A.type == "PReLU")
+                    {
+                        auto pw = wm.find(A.name);
+                        if (pw == wm.end() || pw->second.empty())
+                            return planFail("caffemodel has no slopes for layer " + A.name);
+                        const auto& sl = pw->second[0].data;
+                        if (sl.size() != (size_t)cout && sl.size() != 1)
+                            return planFail("caffemodel: PReLU blob of layer " + A.name + " has the wrong size");
+                        for (int co = 0; co < cout; ++co)
+                            op.hostSlope[co] = sl.size() == 1 ? sl[0] : sl[co];
+                    }
+                    else
+                        return planFail("layer " + A.name + ": unsupported in-place layer type " + A.type);
+                    consumed[lj] = true;
+                    break;
+                }
+                op.out = outputView(L.tops[0], cout, src.level);
+                top.C = cout;
+                top.level = src.level;
+                top.segs.push_back(op.out);
+                net.ops.push_back(std::move(op));
+            }
+            else if (L.type == "Pooling")
+            {
+                if (ins.size() != 1 || ins[0]->isInput || ins[0]->segs.size() != 1)
+                    return planFail("layer " + L.name + ": pooling needs one buffer-backed bottom");
+                if (L.poolMethod != 0 || L.pad != 0)
+                    return planFail("layer " + L.name + ": only unpadded MAX pooling is supported");
+                Level lv;
+                lv.parent = ins[0]->level;
+                lv.k = L.kernel;
+                lv.stride = L.stride;
+                net.levels.push_back(lv);
+                Op op;
+                op.kind = OP_POOL;
+                op.name = L.name;
+                op.level = ins[0]->level;
+                op.outLevel = (int)net.levels.size() - 1;
+                op.in = ins[0]->segs;
+                op.k = L.kernel;
+                op.stride = L.stride;
+                op.out = outputView(L.tops[0], ins[0]->C, op.outLevel);
+                if (op.in[0].C % 8 != 0 || op.in[0].cOff % 8 != 0)
+                    return planFail("layer " + L.name + ": pooled blob must have a multiple of 8 channels");
+                top.C = ins[0]->C;
+                top.level = op.outLevel;
+                top.segs.push_back(op.out);
+                net.ops.push_back(std::move(op));
+            }
+            else if (L.type == "Concat")
+            {
+                if (L.axis != 1)
+                    return planFail("layer " + L.name + ": only channel concatenation (axis 1) is supported");
+                top.level = ins.empty() ? 0 : ins[0]->level;
+                for (const Blob* b : ins)
+                {
+                    if (b->isInput || b->level != top.level)
+                        return planFail("layer " + L.name + ": concat members must be same-size intermediate blobs");
+                    top.C += b->C;
+                }
+                if (owningConcats.count(L.tops[0]))
+                {
+                    View v;
+                    v.buf = concatBuffer.at(L.tops[0]);
+                    v.cOff = 0;
+                    v.C = top.C;
+                    top.segs.push_back(v);
+                }
+                else
+                    for (const Blob* b : ins)
+                        top.segs.insert(top.segs.end(), b->segs.begin(), b->segs.end());
+            }
+            else
+                return planFail("layer " + L.name + ": unsupported layer type " + L.type);
+            net.blobIndex[L.tops[0]] = (int)net.blobs.size();
+            net.blobs.push_back(top);
+        }
+
+        // ---- output blob: members written in fp32 NCHW straight from the producing conv's epilogue ------
+        auto ob = net.blobIndex.find(net.lastBlobName);
+        if (ob == net.blobIndex.end())
+        {
+            setError("The output blob is a nullptr. Did you use the same name than the prototxt? (Used: %s).",
+                     net.lastBlobName.c_str());
+            return OPB200_ERR_INVALID;
+        }
+        net.outBlob = ob->second;
+        const Blob outB = net.blobs[net.outBlob];
+        if (outB.isInput)
+            return planFail("the output blob cannot be the network input");
+        net.outC = outB.C;
+        net.outLevel = outB.level;
+        int cOff = 0;
+        for (const View& seg : outB.segs)
+        {
+            int left = seg.C, segOff = seg.cOff;
+            while (left > 0)   // a segment may span several co-located conv outputs
+            {
+                bool found = false;
+                for (auto& op : net.ops)
+                    if (op.kind == OP_CONV && op.out.buf == seg.buf && op.out.cOff == segOff && op.out.C <= left)
+                    {
+                        op.out32Off = cOff;
+                        cOff += op.out.C;
+                        segOff += op.out.C;
+                        left -= op.out.C;
+                        found = true;
+                        break;
+                    }
+                if (!found)
+                {
+                    Op cv;
+                    cv.kind = OP_CONVERT;
+                    cv.name = net.lastBlobName + "/convert";
+                    cv.level = cv.outLevel = outB.level;
+                    View v = seg;
+                    v.cOff = segOff;
+                    v.C = left;
+                    cv.in.push_back(v);
+                    cv.out32Off = cOff;
+                    cOff += left;
+                    left = 0;
+                    net.ops.push_back(cv);
+                }
+            }
+        }
+        // ---- which conv outputs does anybody read in bf16? ------------------------------------------------
+        for (auto& op : net.ops)
+        {
+            if (op.kind != OP_CONV)
+                continue;
+            bool read = false;
+            for (const auto& other : net.ops)
+                for (const View& v : other.in)
+                    read = read || overlaps(v, op.out);
+            op.storeBf16 = read || op.out32Off < 0;
+        }
+        return OPB200_OK;
+    }
+
+    static opb200_status uploadWeights(Net& net)
+    {
+        for (auto& op : net.ops)
+        {
+            if (op.kind != OP_CONV)
+                continue;
+            OPB_CUDA(cudaMalloc(&op.dW, op.hostW.size() * sizeof(__nv_bfloat16)));
+            OPB_CUDA(cudaMalloc(&op.dBias, op.hostBias.size() * sizeof(float)));
+            OPB_CUDA(cudaMalloc(&op.dSlope, op.hostSlope.size() * sizeof(float)));
+            OPB_CUDA(cudaMemcpy(op.dW, op.hostW.data(), op.hostW.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
+            OPB_CUDA(cudaMemcpy(op.dBias, op.hostBias.data(), op.hostBias.size() * sizeof(float), cudaMemcpyHostToDevice));
+            OPB_CUDA(cudaMemcpy(op.dSlope, op.hostSlope.data(), op.hostSlope.size() * sizeof(float),
+                                cudaMemcpyHostToDevice));
+            std::vector<__nv_bfloat16>().swap(op.hostW);
+        }
+        return OPB200_OK;
+    }
+
+    // ------------------------------------------------------------------------------------------------
+    // reshape: level sizes, arena, tensor maps (reference: reshapeNetCaffe, netCaffe.cpp:105-122)
+    // ------------------------------------------------------------------------------------------------
+    static void chooseTile(int W, int H, int& TW, int& TH)
+    {
+        double best = -1;
+        TW = 8;
+        TH = 16;
+        for (int tw = 128; tw >= 1; tw >>= 1)   // prefer wide tiles on ties
+        {
+            const int th = kConvBlockM / tw;
+            const double tiles = (double)((W + tw - 1) / tw) * ((H + th - 1) / th);
+            const double eff = (double)W * H / (tiles * kConvBlockM);
+            if (eff > best + 1e-9)
+            {
+                best = eff;
+                TW = tw;
+                TH = th;
+            }
+        }
+    }
+
+    static opb200_status reshapeNet(Net& net, int N, int H, int W)
+    {
+        if (net.graphExec)
+        {
+            cudaGraphExecDestroy(net.graphExec);
+            net.graphExec = nullptr;
+        }
+        net.lvH.assign(net.levels.size(), 0);
+        net.lvW.assign(net.levels.size(), 0);
+        net.lvH[0] = H;
+        net.lvW[0] = W;
+        for (size_t l = 1; l < net.levels.size(); ++l)
+        {
+            const Level& lv = net.levels[l];
+            // Caffe pooling output size, pad 0 (pooling_layer.cpp:91-97): ceil((in - k) / stride) + 1
+            auto pooled = [&](int in) {
+                return in < lv.k ? 1 : (int)std::ceil((double)(in - lv.k) / lv.stride) + 1;
+            };
+            net.lvH[l] = pooled(net.lvH[lv.parent]);
+            net.lvW[l] = pooled(net.lvW[lv.parent]);
+        }
+        size_t total = 0;
+        auto carve = [&](size_t bytes) {
+            const size_t at = total;
+            total += (bytes + 1023) / 1024 * 1024;
+            return at;
+        };
+        for (auto& b : net.buffers)
+            b.offset = carve((size_t)N * net.lvH[b.level] * net.lvW[b.level] * b.C * 2);
+        net.inputBytes = (size_t)N * net.inputC * H * W * 4;
+        net.outBytes = (size_t)N * net.outC * net.lvH[net.outLevel] * net.lvW[net.outLevel] * 4;
+        const size_t inOff = carve(net.inputBytes), outOff = carve(net.outBytes);
+        if (total > net.arenaBytes)
+        {
+            if (net.arena)
+                cudaFree(net.arena);
+            net.arena = nullptr;
+            net.arenaBytes = 0;
+            OPB_CUDA(cudaMalloc(&net.arena, total));
+            net.arenaBytes = total;
+        }
+        OPB_CUDA(cudaMemset(net.arena, 0, total));
+        net.dInput = reinterpret_cast<float*>(net.arena + inOff);
+        net.dOut32 = reinterpret_cast<float*>(net.arena + outOff);
+        net.N = N;
+        net.H = H;
+        net.W = W;
+        net.flopsPerForward = 0;
+        auto viewPtr = [&](const View& v) {
+            return net.arena + net.buffers[v.buf].offset + (size_t)v.cOff * 2;
+        };
+        for (auto& op : net.ops)
+        {
+            if (op.kind != OP_CONV)
+                continue;
+            const int h = net.lvH[op.level], w = net.lvW[op.level];
+            ConvParams& p = op.cp;
+            std::memset(&p, 0, sizeof(p));
+            chooseTile(w, h, p.TW, p.TH);
+            p.tilesX = (w + p.TW - 1) / p.TW;
+            p.tilesY = (h + p.TH - 1) / p.TH;
+            p.H = h;
+            p.W = w;
+            p.N = N;
+            p.kh = p.kw = op.k;
+            p.pad = op.pad;
+            p.nSeg = (int)op.in.size();
+            p.chunksTotal = op.chunksTotal;
+            p.nTilesN = op.nTilesN;
+            p.cout = op.cout;
+            p.bias = op.dBias;
+            p.slope = op.dSlope;
+            p.storeBf16 = op.storeBf16 ? 1 : 0;
+            p.out32 = op.out32Off >= 0 ? net.dOut32 : nullptr;
+            p.out32C = net.outC;
+            p.out32Off = op.out32Off >= 0 ? op.out32Off : 0;
+            for (int s = 0; s < p.nSeg; ++s)
+            {
+                p.segChunks[s] = op.segChunks[s];
+                const opb200_status st = makeActivationMap(&p.aMap[s], viewPtr(op.in[s]), op.in[s].C, w, h, N,
+                                                           net.buffers[op.in[s].buf].C, kConvBlockK, p.TW, p.TH, true);
+                if (st != OPB200_OK)
+                    return st;
+            }
+            opb200_status st = makeWeightMap(&p.bMap, op.dW, op.kTotal, op.nTilesN * op.bn, op.bn);
+            if (st != OPB200_OK)
+                return st;
+            st = makeActivationMap(&p.oMap, viewPtr(op.out), op.out.C, w, h, N, net.buffers[op.out.buf].C, 32, p.TW,
+                                   p.TH, false);
+            if (st != OPB200_OK)
+                return st;
+            net.flopsPerForward += op.flopsPerPixel * (double)N * h * w;
+        }
+        return OPB200_OK;
+    }
+
+    // ------------------------------------------------------------------------------------------------
+    // forward
+    // ------------------------------------------------------------------------------------------------
+    struct NetHandle
+    {
+        Net net;
+        cudaStream_t own = nullptr;
+        cudaEvent_t evIn = nullptr, evOut = nullptr;
+        int launchesPerForward = 0;
+    };
+
+    static opb200_status enqueueOps(Net& net, cudaStream_t st, int* launches)
+    {
+        auto viewPtr = [&](const View& v) { return net.arena + net.buffers[v.buf].offset + (size_t)v.cOff * 2; };
+        int n = 0;
+        for (auto& op : net.ops)
+        {
+            opb200_status s = OPB200_OK;
+            const int h = net.lvH[op.level], w = net.lvW[op.level];
+            switch (op.kind)
+            {
+            case OP_PATCH:
+                s = launchInputPatch(viewPtr(op.out), net.dInput, net.N, op.inC, h, w, op.k, op.pad,
+                                     net.buffers[op.out.buf].C, st);
+                break;
+            case OP_CONV: s = launchConv(op.cp, op.bn, net.gridCap, st); break;
+            case OP_POOL:
+                s = launchMaxPool(viewPtr(op.out), viewPtr(op.in[0]), net.N, op.in[0].C, h, w, net.lvH[op.outLevel],
+                                  net.lvW[op.outLevel], op.k, op.stride, net.buffers[op.in[0].buf].C,
+                                  net.buffers[op.out.buf].C, st);
+                break;
+            case OP_CONVERT:
+                s = launchNhwcToNchw(net.dOut32, viewPtr(op.in[0]), net.N, op.in[0].C, h, w,
+                                     net.buffers[op.in[0].buf].C, net.outC, op.out32Off, st);
+                break;
+            }
+            if (s != OPB200_OK)
+                return s;
+            ++n;
+        }
+        if (launches)
+            *launches = n;
+        return OPB200_OK;
+    }
+
+    static opb200_status forwardNet(NetHandle& h, const float* input, bool onDevice, int N, int C, int H, int W,
+                                    cudaStream_t user)
+    {
+        Net& net = h.net;
+        OPB_CUDA(cudaSetDevice(net.gpu));
+        if (N != net.N || H != net.H || W != net.W)
+        {
+            const opb200_status s = reshapeNet(net, N, H, W);
+            if (s != OPB200_OK)
+                return s;
+        }
+        // fork from the caller's stream onto the net's own (capturable) stream
+        OPB_CUDA(cudaEventRecord(h.evIn, user));
+        OPB_CUDA(cudaStreamWaitEvent(h.own, h.evIn, 0));
+        OPB_CUDA(cudaMemcpyAsync(net.dInput, input, net.inputBytes,
+                                 onDevice ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, h.own));
+        if (net.useGraph)
+        {
+            if (!net.graphExec)
+            {
+                // warm launch outside capture (sets function attributes, surfaces launch errors early)
+                opb200_status s = enqueueOps(net, h.own, &h.launchesPerForward);
+                if (s != OPB200_OK)
+                    return s;
+                OPB_CUDA(cudaStreamSynchronize(h.own));
+                cudaGraph_t graph = nullptr;
+                OPB_CUDA(cudaStreamBeginCapture(h.own, cudaStreamCaptureModeThreadLocal));
+                s = enqueueOps(net, h.own, nullptr);
+                const cudaError_t e = cudaStreamEndCapture(h.own, &graph);
+                if (s != OPB200_OK)
+                    return s;
+                OPB_CUDA(e);
+                OPB_CUDA(cudaGraphInstantiate(&net.graphExec, graph, 0));
+                OPB_CUDA(cudaGraphDestroy(graph));
+            }
+            OPB_CUDA(cudaGraphLaunch(net.graphExec, h.own));
+        }
+        else
+        {
+            const opb200_status s = enqueueOps(net, h.own, &h.launchesPerForward);
+            if (s != OPB200_OK)
+                return s;
+        }
+        OPB_CUDA(cudaEventRecord(h.evOut, h.own));
+        OPB_CUDA(cudaStreamWaitEvent(user, h.evOut, 0));
+        return OPB200_OK;
+    }
+}
+
+// ----------------------------------------------------------------------------------------------------
+// C ABI (include/opb200.h)
+// ----------------------------------------------------------------------------------------------------
+using namespace opb;
+
+struct opb200_net
+{
+    NetHandle h;
+};
+
+static bool fileExists(const char* p)
+{
+    FILE* f = p ? std::fopen(p, "rb") : nullptr;
+    if (f)
+        std::fclose(f);
+    return f != nullptr;
+}
+
+extern "C" opb200_status opb200_net_create(opb200_net** out, const char* prototxt, const char* caffemodel, int gpu_id,
+                                           const char* last_blob_name)
+{
+    OPB_REQUIRE(out && prototxt && caffemodel, "net_create: null argument");
+    *out = nullptr;
+    // same wording as NetCaffe's constructor checks (reference: src/openpose/net/netCaffe.cpp:55-66)
+    static const char* hint =
+        ".\nPossible causes:\n\t1. Not downloading the OpenPose trained models.\n\t2. Not running OpenPose from the "
+        "root directory (i.e., where the `model` folder is located, but do not move the `model` folder!).\n\t3. Using "
+        "paths with spaces.";
+    if (!fileExists(prototxt))
+    {
+        setError("Prototxt file not found: %s%s", prototxt, hint);
+        return OPB200_ERR_IO;
+    }
+    if (!fileExists(caffemodel))
+    {
+        setError("Caffe trained model file not found: %s%s", caffemodel, hint);
+        return OPB200_ERR_IO;
+    }
+    std::unique_ptr<opb200_net> n(new opb200_net());
+    Net& net = n->h.net;
+    net.gpu = gpu_id;
+    net.lastBlobName = (last_blob_name && *last_blob_name) ? last_blob_name : "net_output";
+    net.useGraph = std::getenv("OPB200_NO_GRAPH") == nullptr;
+    if (const char* g = std::getenv("OPB200_GRID_CAP"))
+        net.gridCap = std::max(1, std::atoi(g));
+    std::string text, err;
+    if (!readFile(prototxt, text) || !parsePrototxt(text, net.def, err))
+    {
+        setError("%s (%s)", err.empty() ? "prototxt: cannot read file" : err.c_str(), prototxt);
+        return OPB200_ERR_IO;
+    }
+    WeightMap wm;
+    if (!readCaffemodel(caffemodel, wm, err))
+    {
+        setError("%s", err.c_str());
+        return OPB200_ERR_IO;
+    }
+    opb200_status s = planNet(net, wm);
+    if (s != OPB200_OK)
+        return s;
+    OPB_CUDA(cudaSetDevice(gpu_id));
+    s = uploadWeights(net);
+    if (s != OPB200_OK)
+        return s;
+    OPB_CUDA(cudaStreamCreateWithFlags(&n->h.own, cudaStreamNonBlocking));
+    OPB_CUDA(cudaEventCreateWithFlags(&n->h.evIn, cudaEventDisableTiming));
+    OPB_CUDA(cudaEventCreateWithFlags(&n->h.evOut, cudaEventDisableTiming));
+    *out = n.release();
+    return OPB200_OK;
+}
+
+extern "C" void opb200_net_destroy(opb200_net* n)
+{
+    if (!n)
+        return;
+    cudaSetDevice(n->h.net.gpu);
+    if (n->h.own)
+    {
+        cudaStreamSynchronize(n->h.own);
+        cudaStreamDestroy(n->h.own);
+    }
+    if (n->h.evIn)
+        cudaEventDestroy(n->h.evIn);
+    if (n->h.evOut)
+        cudaEventDestroy(n->h.evOut);
+    delete n;
+}
+
+extern "C" opb200_status opb200_net_forward(opb200_net* n, const float* input, int input_on_device,
+                                            const int shape[4], void* stream)
+{
+    OPB_REQUIRE(n != nullptr, "net_forward: null net");
+    // same checks and wording as NetCaffe::forwardPass (reference: src/openpose/net/netCaffe.cpp:218-222)
+    if (!input || !shape || shape[0] <= 0 || shape[2] <= 0 || shape[3] <= 0)
+    {
+        setError("The Array inputData cannot be empty.");
+        return OPB200_ERR_INVALID;
+    }
+    if (shape[1] != n->h.net.inputC)
+    {
+        setError("The Array inputData must have 4 dimensions: [batch size, 3 (RGB), height, width].");
+        return OPB200_ERR_INVALID;
+    }
+    return forwardNet(n->h, input, input_on_device != 0, shape[0], shape[1], shape[2], shape[3],
+                      static_cast<cudaStream_t>(stream));
+}
+
+extern "C" opb200_status opb200_net_output(opb200_net* n, const float** dev_ptr, int shape[4])
+{
+    OPB_REQUIRE(n && dev_ptr && shape, "net_output: null argument");
+    Net& net = n->h.net;
+    OPB_REQUIRE(net.N > 0, "net_output: forward has not run yet");
+    *dev_ptr = net.dOut32;
+    shape[0] = net.N;
+    shape[1] = net.outC;
+    shape[2] = net.lvH[net.outLevel];
+    shape[3] = net.lvW[net.outLevel];
+    return OPB200_OK;
+}
+
+extern "C" opb200_status opb200_net_info(opb200_net* n, opb200_net_info_t* info)
+{
+    OPB_REQUIRE(n && info, "net_info: null argument");
+    Net& net = n->h.net;
+    int convs = 0;
+    for (const auto& op : net.ops)
+        convs += op.kind == OP_CONV;
+    info->conv_layers = convs;
+    info->kernel_launches_per_forward = (int)net.ops.size();
+    info->flops_per_forward = net.flopsPerForward;
+    info->arena_bytes = (double)net.arenaBytes;
+    info->output_channels = net.outC;
+    return OPB200_OK;
+}
+
+// Test hook: copy any intermediate blob (bf16 NHWC views) to a host fp32 NCHW array. Synchronises the device.
+extern "C" opb200_status opb200_net_read_blob(opb200_net* n, const char* name, float* host_nchw, size_t capacity,
+                                              int shape[4])
+{
+    OPB_REQUIRE(n && name && shape, "net_read_blob: null argument");
+    Net& net = n->h.net;
+    auto it = net.blobIndex.find(name);
+    if (it == net.blobIndex.end() || net.blobs[it->second].isInput)
+    {
+        setError("net_read_blob: no intermediate blob named %s", name);
+        return OPB200_ERR_INVALID;
+    }
+    OPB_REQUIRE(net.N > 0, "net_read_blob: forward has not run yet");
+    const Blob& b = net.blobs[it->second];
+    const int h = net.lvH[b.level], w = net.lvW[b.level];
+    shape[0] = net.N;
+    shape[1] = b.C;
+    shape[2] = h;
+    shape[3] = w;
+    const size_t count = (size_t)net.N * b.C * h * w;
+    if (!host_nchw)
+        return OPB200_OK;   // shape query
+    OPB_REQUIRE(capacity >= count, "net_read_blob: host buffer too small");
+    OPB_CUDA(cudaSetDevice(net.gpu));
+    OPB_CUDA(cudaDeviceSynchronize());
+    float* tmp = nullptr;
+    OPB_CUDA(cudaMalloc(&tmp, count * sizeof(float)));
+    int cOff = 0;
+    opb200_status s = OPB200_OK;
+    for (const View& v : b.segs)
+    {
+        s = launchNhwcToNchw(tmp, net.arena + net.buffers[v.buf].offset + (size_t)v.cOff * 2, net.N, v.C, h, w,
+                             net.buffers[v.buf].C, b.C, cOff, nullptr);
+        if (s != OPB200_OK)
+            break;
+        cOff += v.C;
+    }
+    if (s == OPB200_OK)
+    {
+        const cudaError_t e = cudaMemcpy(host_nchw, tmp, count * sizeof(float), cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess)
+        {
+            setError("CUDA error %s in net_read_blob", cudaGetErrorName(e));
+            s = OPB200_ERR_CUDA;
+        }
+    }
+    cudaFree(tmp);
+    return s;
+}
+
+// Host-only: parse + plan, no CUDA call. Writes one line per planned op into `text` (for tests and debugging):
+//   conv <name> cin cout k bn tilesN segs=[buf:off:C,...] out=buf:off:C out32=<off|-1> bf16=<0|1>
+extern "C" opb200_status opb200_net_describe(const char* prototxt, const char* caffemodel, const char* last_blob_name,
+                                             char* text, size_t capacity)
+{
+    OPB_REQUIRE(prototxt && caffemodel && text && capacity > 0, "net_describe: null argument");
+    Net net;
+    net.lastBlobName = (last_blob_name && *last_blob_name) ? last_blob_name : "net_output";
+    std::string src, err;
+    if (!readFile(prototxt, src) || !parsePrototxt(src, net.def, err))
+    {
+        setError("%s (%s)", err.empty() ? "prototxt: cannot read file" : err.c_str(), prototxt);
+        return OPB200_ERR_IO;
+    }
+    WeightMap wm;
+    if (!readCaffemodel(caffemodel, wm, err))
+    {
+        setError("%s", err.c_str());
+        return OPB200_ERR_IO;
+    }
+    const opb200_status s = planNet(net, wm);
+    if (s != OPB200_OK)
+        return s;
+    std::string out;
+    char line[1024];
+    static const char* kinds[] = {"patch", "conv", "pool", "convert"};
+    for (const auto& op : net.ops)
+    {
+        std::string segs;
+        for (const View& v : op.in)
+        {
+            std::snprintf(line, sizeof(line), "%s%d:%d:%d", segs.empty() ? "" : ",", v.buf, v.cOff, v.C);
+            segs += line;
+        }
+        std::snprintf(line, sizeof(line), "%s %s cin=%d cout=%d k=%d bn=%d tilesN=%d segs=[%s] out=%d:%d:%d out32=%d bf16=%d\n",
+                      kinds[op.kind], op.name.c_str(), op.cin, op.cout, op.k, op.bn, op.nTilesN, segs.c_str(),
+                      op.out.buf, op.out.cOff, op.out.C, op.out32Off, op.storeBf16 ? 1 : 0);
+        out += line;
+    }
+    std::snprintf(line, sizeof(line), "output %s C=%d buffers=%d levels=%d\n", net.lastBlobName.c_str(), net.outC,
+                  (int)net.buffers.size(), (int)net.levels.size());
+    out += line;
+    if (out.size() + 1 > capacity)
+        OPB_FAIL(OPB200_ERR_INVALID, "net_describe: text buffer too small");
+    std::memcpy(text, out.c_str(), out.size() + 1);
+    return OPB200_OK;
+}

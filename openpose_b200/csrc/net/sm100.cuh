@@ -1,0 +1,171 @@
+// sm_100a primitives used by the implicit-GEMM convolution: mbarrier, TMA (cp.async.bulk.tensor), TMEM
+// allocation, tcgen05.mma / commit / ld, UMMA descriptors. Inline PTX only; compiled for sm_100a.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace opb
+{
+namespace sm100
+{
+    __device__ __forceinline__ uint32_t smemAddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+    __device__ __forceinline__ bool electOne()
+    {
+        uint32_t pred = 0;
+        asm volatile(
+            "{\n\t.reg .pred P;\n\t"
+            "elect.sync _|P, 0xffffffff;\n\t"
+            "selp.u32 %0, 1, 0, P;\n\t}"
+            : "=r"(pred));
+        return pred != 0;
+    }
+
+    // ---------------------------------------------------------------- mbarrier
+    __device__ __forceinline__ void mbarInit(uint64_t* bar, uint32_t count)
+    {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smemAddr(bar)), "r"(count));
+    }
+    __device__ __forceinline__ void fenceBarrierInit()
+    {
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __device__ __forceinline__ void mbarExpectTx(uint64_t* bar, uint32_t bytes)
+    {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smemAddr(bar)), "r"(bytes)
+                     : "memory");
+    }
+    __device__ __forceinline__ void mbarArrive(uint64_t* bar)
+    {
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smemAddr(bar)) : "memory");
+    }
+    __device__ __forceinline__ bool mbarTryWait(uint64_t* bar, uint32_t parity)
+    {
+        uint32_t done;
+        asm volatile(
+            "{\n\t.reg .pred P;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, P;\n\t}"
+            : "=r"(done)
+            : "r"(smemAddr(bar)), "r"(parity)
+            : "memory");
+        return done != 0;
+    }
+    __device__ __forceinline__ void mbarWait(uint64_t* bar, uint32_t parity)
+    {
+        while (!mbarTryWait(bar, parity)) {}
+    }
+
+    // ---------------------------------------------------------------- TMA
+    __device__ __forceinline__ void prefetchTensorMap(const CUtensorMap* m)
+    {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
+    }
+    __device__ __forceinline__ void tmaLoad2d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1)
+    {
+        asm volatile(
+            "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+            ::"r"(smemAddr(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smemAddr(bar)), "r"(c0), "r"(c1)
+            : "memory");
+    }
+    __device__ __forceinline__ void tmaLoad4d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
+                                              int c3)
+    {
+        asm volatile(
+            "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+            ::"r"(smemAddr(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smemAddr(bar)), "r"(c0), "r"(c1), "r"(c2),
+            "r"(c3)
+            : "memory");
+    }
+    __device__ __forceinline__ void tmaStore4d(const CUtensorMap* m, const void* src, int c0, int c1, int c2, int c3)
+    {
+        asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                     ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smemAddr(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                     : "memory");
+    }
+    __device__ __forceinline__ void tmaStoreCommit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+    __device__ __forceinline__ void tmaStoreWaitRead0()
+    {
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    }
+    __device__ __forceinline__ void tmaStoreWaitAll() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+    // generic-proxy smem writes -> visible to the async proxy (TMA store reads them)
+    __device__ __forceinline__ void fenceProxyAsyncShared()
+    {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+
+    // ---------------------------------------------------------------- TMEM + tcgen05
+    template <uint32_t kCols>
+    __device__ __forceinline__ void tmemAlloc(uint32_t* dstSmem)
+    {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smemAddr(dstSmem)),
+                     "n"(kCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    template <uint32_t kCols>
+    __device__ __forceinline__ void tmemFree(uint32_t taddr)
+    {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+    }
+    __device__ __forceinline__ void tcFenceBefore() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+    __device__ __forceinline__ void tcFenceAfter() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+    // D[tmem] (+)= A[smem] * B[smem]; kind::f16 covers bf16 inputs with fp32 accumulation.
+    __device__ __forceinline__ void mmaBf16(uint32_t tmemD, uint64_t descA, uint64_t descB, uint32_t idesc,
+                                            uint32_t accumulate)
+    {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(tmemD), "l"(descA), "l"(descB), "r"(idesc), "r"(accumulate)
+            : "memory");
+    }
+    // Arrive on an mbarrier once every previously issued tcgen05.mma of this thread has completed.
+    __device__ __forceinline__ void mmaCommit(uint64_t* bar)
+    {
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smemAddr(bar))
+                     : "memory");
+    }
+    // 32 lanes x 32 consecutive fp32 columns -> 32 registers per thread (thread = lane = accumulator row).
+    __device__ __forceinline__ void tmemLoad32(uint32_t taddr, uint32_t (&v)[32])
+    {
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+              "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+              "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+              "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+            : "r"(taddr));
+    }
+    __device__ __forceinline__ void tmemLoadWait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+    // UMMA shared-memory descriptor, K-major operand, 128-byte swizzle, rows of 64 bf16 (=128 B), 8-row
+    // groups 1024 B apart (SBO). Field layout: cute/arch/mma_sm100_desc.hpp SmemDescriptor (version 1).
+    __device__ __forceinline__ uint64_t smemDescSw128(uint32_t saddr)
+    {
+        uint64_t d = 0;
+        d |= (uint64_t)((saddr & 0x3FFFF) >> 4);          // start address, bits [0,14)
+        d |= (uint64_t)0 << 16;                           // leading byte offset: unused for swizzled K-major
+        d |= (uint64_t)(1024 >> 4) << 32;                 // stride byte offset, bits [32,46)
+        d |= (uint64_t)1 << 46;                           // descriptor version (sm_100)
+        d |= (uint64_t)2 << 61;                           // layout type SWIZZLE_128B
+        return d;
+    }
+    // Instruction descriptor: D=f32, A=B=bf16, both K-major, M x N tile (InstrDescriptor, same header).
+    __host__ __device__ constexpr uint32_t instrDescBf16(uint32_t m, uint32_t n)
+    {
+        return (1u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((m >> 4) << 24);
+    }
+
+    __device__ __forceinline__ void namedBarrier(uint32_t id, uint32_t threads)
+    {
+        asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+    }
+}
+}
