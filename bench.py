@@ -264,9 +264,12 @@ def run_gpu(args):
         return x
 
     def step_host():
-        d = dev_in
-        d.copy_(host_in, non_blocking=True)
-        out = step_device()
+        if have_net:   # the public call takes the HOST array (as op::Net::forwardPass does); H2D happens inside it
+            x = net.forward_device(host_in)
+            out = post.run(x) if post is not None else x
+        else:
+            dev_in.copy_(host_in, non_blocking=True)
+            out = step_device()
         if post is not None:
             h_kp.copy_(out[0], non_blocking=True)
             h_sc.copy_(out[1], non_blocking=True)
@@ -454,7 +457,7 @@ def main():
         run_gpu(args)
 
 
-DEFAULT_STAGES = "post"
+DEFAULT_STAGES = "full"
 
 if __name__ == "__main__":
     main()

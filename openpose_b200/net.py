@@ -172,3 +172,21 @@ def bench_net(batch: int, h: int, w: int, device, model: str = "body_25", seed: 
     net = NetB200(proto, cm, gpuId=device.index or 0)
     net.initializationOnThread()
     return _BenchNet(net, batch)
+
+
+def smoke() -> None:
+    """One small BODY_25 forward on cuda:0 checked against the FP32 CPU oracle (called by __graft_entry__.smoke)."""
+    import torch
+    from oracle import ref_net
+    from . import synth
+    proto, cm, ref = ref_net.build("body_25", 1234)
+    x = synth.frames_to_net_input(synth.frames(1, 64, 96, 3))
+    net = NetB200(proto, cm)
+    net.initializationOnThread()
+    net.forwardPass(x)
+    got = net.getOutputBlobArray().cpu().numpy()
+    want = ref.forward(x, keep=["net_output"])["net_output"]
+    err = float(np.abs(got - want).max())
+    assert got.shape == want.shape and err <= 2e-2, "NetB200 differs from the oracle: max-abs %g" % err
+    print("net smoke ok: BODY_25 64x96, %d conv launches, max-abs vs fp32 oracle %.4f" % (net.info().conv_layers, err))
+    net.close()

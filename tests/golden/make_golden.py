@@ -40,3 +40,16 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+def make_prototxt_signatures():
+    """tests/golden/prototxt_signatures.json: sha256 of the canonical layer list of the REFERENCE's four deploy
+    prototxts (needs /root/reference); tests/test_net_cpu.py compares openpose_b200.protogen's output to them."""
+    import json
+    from oracle import caffe_io
+    from openpose_b200 import protogen
+    from tests.test_net_cpu import SIG_FILE, _signature
+    sigs = {m: _signature(caffe_io.load_netdef("/root/reference/" + protogen.REFERENCE_FILES[m]))
+            for m in protogen.MODELS}
+    with open(SIG_FILE, "w") as f:
+        json.dump(sigs, f, indent=1)

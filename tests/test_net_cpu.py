@@ -1,0 +1,151 @@
+"""CPU tests of the net path's host logic (no GPU): generated graphs vs the reference's prototxt files,
+the oracle's layer semantics (KATs restated from Caffe's own tests), the C++ prototxt/caffemodel readers and
+graph planner (through the host-only C-ABI entry opb200_net_describe) vs the Python oracle readers."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from openpose_b200 import net as netmod
+from openpose_b200 import protogen
+from openpose_b200._lib import Opb200Error
+from oracle import caffe_io, ref_net
+
+REF = "/root/reference"
+SIG_FILE = os.path.join(os.path.dirname(__file__), "golden", "prototxt_signatures.json")
+
+
+def _signature(nd: caffe_io.NetDef) -> str:
+    rows = [[L.name, L.type, L.bottoms, L.tops, {k: (v if not isinstance(v, bool) else int(v))
+                                                  for k, v in sorted(L.params.items())}] for L in nd.layers]
+    blob = json.dumps([nd.name, nd.inputs, rows], sort_keys=True).encode()
+    return hashlib.sha256(blob).hexdigest()
+
+
+@pytest.mark.parametrize("model", protogen.MODELS)
+def test_generated_prototxt_equals_reference(model):
+    gen = caffe_io.load_netdef(protogen.generate(model))
+    with open(SIG_FILE) as f:
+        sigs = json.load(f)
+    assert _signature(gen) == sigs[model]            # committed signature of the reference's file
+    path = os.path.join(REF, protogen.REFERENCE_FILES[model])
+    if os.path.exists(path):                         # and the file itself, where the reference tree exists
+        ref = caffe_io.load_netdef(path)
+        assert _signature(ref) == sigs[model]
+        assert [(L.name, L.type, L.bottoms, L.tops, L.params) for L in ref.layers] == \
+               [(L.name, L.type, L.bottoms, L.tops, L.params) for L in gen.layers]
+
+
+# ---- oracle KATs (specifications restated from 3rdparty/caffe/src/caffe/test/) ---------------------------
+def _one_layer_net(layer_text, cin):
+    return caffe_io.load_netdef('input: "image"\ninput_dim: 1\ninput_dim: %d\ninput_dim: 4\ninput_dim: 4\n' % cin + layer_text)
+
+
+def test_oracle_conv_matches_naive_definition():
+    """test_convolution_layer.cpp:22-147 (caffe_conv reference loop): cross-correlation with zero padding."""
+    rng = np.random.default_rng(0)
+    nd = _one_layer_net('layer { name: "c" type: "Convolution" bottom: "image" top: "net_output" '
+                        'convolution_param { num_output: 4 pad: 1 kernel_size: 3 } }', 3)
+    w = rng.standard_normal((4, 3, 3, 3)).astype(np.float32)
+    b = rng.standard_normal(4).astype(np.float32)
+    x = rng.standard_normal((2, 3, 5, 6)).astype(np.float32)
+    got = ref_net.RefNet(nd, {"c": [w, b]}).forward(x)["net_output"]
+    want = np.zeros((2, 4, 5, 6), np.float64)
+    xp = np.pad(x, ((0, 0), (0, 0), (1, 1), (1, 1)))
+    for n in range(2):
+        for o in range(4):
+            for y in range(5):
+                for xx in range(6):
+                    want[n, o, y, xx] = (xp[n, :, y:y + 3, xx:xx + 3].astype(np.float64) * w[o]).sum() + b[o]
+    assert np.abs(got - want).max() < 1e-5
+
+
+def test_oracle_sobel_kat():
+    """test_convolution_layer.cpp:498-589: a 3x3 Sobel filter equals its separable (3x1)*(1x3) form."""
+    x = np.random.default_rng(1).standard_normal((1, 1, 8, 9)).astype(np.float32)
+    sobel = np.array([[-1, 0, 1], [-2, 0, 2], [-1, 0, 1]], np.float32).reshape(1, 1, 3, 3)
+    nd = _one_layer_net('layer { name: "c" type: "Convolution" bottom: "image" top: "net_output" '
+                        'convolution_param { num_output: 1 pad: 1 kernel_size: 3 } }', 1)
+    got = ref_net.RefNet(nd, {"c": [sobel, np.zeros(1, np.float32)]}).forward(x)["net_output"][0, 0]
+    xp = np.pad(x[0, 0], 1)
+    col = xp[:-2] + 2 * xp[1:-1] + xp[2:]                   # (1,2,1)^T along y
+    want = col[:, 2:] - col[:, :-2]                         # (-1,0,1) along x
+    assert np.abs(got - want).max() < 1e-5
+
+
+def test_oracle_prelu_closed_form_and_ceil_pool():
+    """test_neuron_layer.cpp:124-150,786-803 (PReLU = max(x,0)+a_c*min(x,0)); test_pooling_layer.cpp (2x2 stride 2
+    MAX pooling uses the CEIL output size and clips windows at the border)."""
+    x = np.random.default_rng(2).standard_normal((1, 3, 5, 7)).astype(np.float32)
+    nd = _one_layer_net('layer { name: "p" type: "PReLU" bottom: "image" top: "image" }\n'
+                        'layer { name: "q" type: "Pooling" bottom: "image" top: "net_output" '
+                        'pooling_param { pool: MAX kernel_size: 2 stride: 2 } }', 3)
+    a = np.array([0.25, 0.1, 0.5], np.float32)
+    got = ref_net.RefNet(nd, {"p": [a]}).forward(x)["net_output"]
+    y = np.maximum(x, 0) + a[None, :, None, None] * np.minimum(x, 0)
+    assert got.shape == (1, 3, 3, 4)                        # ceil(5/2), ceil(7/2)
+    for i in range(3):
+        for j in range(4):
+            assert np.array_equal(got[0, :, i, j], y[0, :, 2 * i:2 * i + 2, 2 * j:2 * j + 2].max(axis=(1, 2)))
+
+
+# ---- C++ readers + planner (host-only ABI entry) vs the oracle readers -----------------------------------
+@pytest.mark.parametrize("model", protogen.MODELS)
+def test_cpp_planner_covers_every_layer(model):
+    proto, cm, ref = ref_net.build(model, 1234)
+    text = netmod.describe(proto, cm)
+    lines = text.strip().splitlines()
+    convs = [l.split() for l in lines if l.startswith("conv ")]
+    nd = ref.netdef
+    want = [L for L in nd.layers if L.type == "Convolution"]
+    assert [c[1] for c in convs] == [L.name for L in want]
+    blobs = caffe_io.read_caffemodel(cm)
+    for c, L in zip(convs, want):
+        kv = dict(t.split("=", 1) for t in c[2:])
+        assert int(kv["cout"]) == L.params["num_output"] == blobs[L.name][0].shape[0]
+        assert int(kv["cin"]) == blobs[L.name][0].shape[1]
+        segs = [tuple(int(v) for v in s.split(":")) for s in kv["segs"].strip("[]").split(",")]
+        if L.bottoms[0] != "image":
+            assert sum(s[2] for s in segs) == int(kv["cin"])          # concat segments cover the input channels
+        assert all(s[1] % 8 == 0 for s in segs)                      # 16-byte aligned TMA bases
+    assert sum(1 for l in lines if l.startswith("pool ")) == 3
+    assert lines[-1].startswith("output net_output C=%d " % protogen.OUTPUT_CHANNELS[model])
+    # every member of net_output is written in fp32 by a conv epilogue (no convert pass needed)
+    assert not any(l.startswith("convert ") for l in lines)
+    assert sum(int(dict(t.split("=", 1) for t in c[2:])["out32"]) >= 0 for c in convs) == (2 if model in ("body_25", "coco") else 1)
+
+
+def test_cpp_reader_error_paths(tmp_path):
+    proto, cm, _ = ref_net.build("hand", 1234)
+    with pytest.raises(Opb200Error, match="output blob is a nullptr"):
+        netmod.describe(proto, cm, "nope")
+    bad = tmp_path / "bad.prototxt"
+    bad.write_text('input: "image"\ninput_dim: 1\ninput_dim: 3\ninput_dim: 8\ninput_dim: 8\n'
+                   'layer { name: "x" type: "Deconvolution" bottom: "image" top: "net_output" }\n')
+    with pytest.raises(Opb200Error, match="unsupported layer type Deconvolution"):
+        netmod.describe(str(bad), cm)
+    trunc = tmp_path / "trunc.caffemodel"
+    trunc.write_bytes(open(cm, "rb").read()[:1000])
+    with pytest.raises(Opb200Error, match="caffemodel"):
+        netmod.describe(proto, str(trunc))
+    strided = tmp_path / "strided.prototxt"
+    strided.write_text('input: "image"\ninput_dim: 1\ninput_dim: 3\ninput_dim: 8\ninput_dim: 8\n'
+                       'layer { name: "conv1_1" type: "Convolution" bottom: "image" top: "net_output" '
+                       'convolution_param { num_output: 64 kernel_size: 3 pad: 1 stride: 2 } }\n')
+    with pytest.raises(Opb200Error, match="only stride-1"):
+        netmod.describe(str(strided), cm)
+
+
+def test_random_init_is_seeded_and_caffemodel_roundtrips(tmp_path):
+    nd = caffe_io.load_netdef(protogen.generate("body_25"))
+    a, b = ref_net.random_init(nd, 7), ref_net.random_init(nd, 7)
+    assert all(np.array_equal(x, y) for k in a for x, y in zip(a[k], b[k]))
+    p = str(tmp_path / "m.caffemodel")
+    ref_net.save_caffemodel(p, nd, a)
+    back = caffe_io.read_caffemodel(p)
+    assert set(back) == set(a)
+    assert all(np.array_equal(x, y) for k in a for x, y in zip(a[k], back[k]))
+    assert sum(x.size for k in a for x in a[k]) > 26_000_000          # BODY_25: 26.15 M parameters

@@ -1,0 +1,150 @@
+"""GPU parity: NetB200 (tcgen05 implicit-GEMM convs, through the C ABI) vs the FP32 CPU restatement of Caffe.
+
+Tolerances (BASELINE.json north star): net output max-abs <= 2e-2 against the FP32 oracle with heat-map-like
+output magnitudes (random-init stage outputs have RMS ~0.05-0.15, see oracle/ref_net.random_init).
+Small synthetic graphs exercise each structural case of the planner/kernel at tight tolerance against the
+bf16-rounding twin of the oracle (same arithmetic: bf16 inputs/weights, fp32 accumulation).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from openpose_b200 import protogen, synth
+from openpose_b200._lib import Opb200Error
+from openpose_b200.net import NetB200
+from oracle import caffe_io, ref_net
+
+pytestmark = pytest.mark.gpu
+TOL_NET = 2e-2
+
+
+def _layer(name, typ, bottoms, top, extra=""):
+    b = "".join('  bottom: "%s"\n' % x for x in bottoms)
+    return 'layer {\n  name: "%s"\n  type: "%s"\n%s  top: "%s"\n%s}\n' % (name, typ, b, top, extra)
+
+
+def _conv(name, bottom, cout, k, top=None):
+    return _layer(name, "Convolution", [bottom], top or name,
+                  "  convolution_param {\n    num_output: %d\n    pad: %d\n    kernel_size: %d\n  }\n" % (cout, k // 2, k))
+
+
+def _build_custom(tmp_path, text, seed=3):
+    nd = caffe_io.load_netdef(text)
+    blobs = ref_net.random_init(nd, seed, out_rms=0.5)
+    proto, cm = str(tmp_path / "n.prototxt"), str(tmp_path / "n.caffemodel")
+    with open(proto, "w") as f:
+        f.write(text)
+    ref_net.save_caffemodel(cm, nd, blobs)
+    return proto, cm, ref_net.RefNet(nd, blobs)
+
+
+def _run(proto, cm, x, last="net_output"):
+    net = NetB200(proto, cm, lastBlobName=last)
+    net.initializationOnThread()
+    net.forwardPass(x)
+    out = net.getOutputBlobArray().cpu().numpy()
+    return net, out
+
+
+HEAD = 'input: "image"\ninput_dim: 1\ninput_dim: 3\ninput_dim: 16\ninput_dim: 16\n'
+
+CASES = {
+    # first-layer patch path + 3x3 + relu, odd sizes (edge tiles, ceil pooling)
+    "trunk_odd": (HEAD + _conv("c1", "image", 64, 3) + _layer("r1", "ReLU", ["c1"], "c1") +
+                  _conv("c2", "c1", 64, 3) + _layer("r2", "PReLU", ["c2"], "c2") +
+                  _layer("p", "Pooling", ["c2"], "p", "  pooling_param {\n    pool: MAX\n    kernel_size: 2\n    stride: 2\n  }\n") +
+                  _conv("c3", "p", 40, 3, top="net_output"), (2, 37, 51)),
+    # dense block: co-located concat, 96-wide (1.5 k-chunks), BN=96; 1x1 with 2 N-tiles; odd Cout
+    "dense96": (HEAD + _conv("c1", "image", 96, 3) + _layer("a1", "PReLU", ["c1"], "c1") +
+                _conv("d0", "c1", 96, 3) + _layer("a2", "PReLU", ["d0"], "d0") +
+                _conv("d1", "d0", 96, 3) + _layer("a3", "PReLU", ["d1"], "d1") +
+                _conv("d2", "d1", 96, 3) + _layer("a4", "PReLU", ["d2"], "d2") +
+                _layer("cat", "Concat", ["d0", "d1", "d2"], "cat", "  concat_param {\n    axis: 1\n  }\n") +
+                _conv("m6", "cat", 256, 1) + _layer("a5", "PReLU", ["m6"], "m6") +
+                _conv("m7", "m6", 52, 1, top="net_output"), (1, 46, 82)),
+    # virtual concat with 3 unaligned segments (COCO style), 7x7 convs, output = concat of two convs
+    "virtual7x7": (HEAD + _conv("f", "image", 128, 3) + _layer("rf", "ReLU", ["f"], "f") +
+                   _conv("l1", "f", 38, 1) + _conv("l2", "f", 19, 1) +
+                   _layer("cat", "Concat", ["l1", "l2", "f"], "cat", "  concat_param {\n    axis: 1\n  }\n") +
+                   _conv("m1", "cat", 128, 7) + _layer("r1", "ReLU", ["m1"], "m1") +
+                   _conv("m2", "cat", 128, 7) + _layer("r2", "ReLU", ["m2"], "m2") +
+                   _conv("o1", "m1", 38, 1) + _conv("o2", "m2", 19, 1) +
+                   _layer("out", "Concat", ["o2", "o1"], "net_output", "  concat_param {\n    axis: 1\n  }\n"), (3, 20, 33)),
+    # wide layers: Cout 512 (4 N-tiles), K = 512*9
+    "wide512": (HEAD + _conv("c1", "image", 256, 3) + _layer("r1", "ReLU", ["c1"], "c1") +
+                _conv("c2", "c1", 512, 3) + _layer("r2", "ReLU", ["c2"], "c2") +
+                _conv("c3", "c2", 512, 3) + _layer("r3", "PReLU", ["c3"], "c3") +
+                _conv("c4", "c3", 71, 1, top="net_output"), (1, 24, 40)),
+}
+
+
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_small_graphs_match_bf16_twin(tmp_path, cuda, case):
+    text, (n, h, w) = CASES[case]
+    proto, cm, ref = _build_custom(tmp_path, text)
+    x = synth.frames_to_net_input(synth.frames(n, h, w, 11))
+    net, got = _run(proto, cm, x)
+    want16 = ref.forward(x, keep=["net_output"], bf16_activations=True)["net_output"]
+    want32 = ref.forward(x, keep=["net_output"])["net_output"]
+    assert got.shape == want32.shape
+    rms = float(np.sqrt((want32 ** 2).mean()))
+    assert np.isfinite(got).all()
+    # same arithmetic up to accumulation order and bf16 re-rounding of intermediates
+    assert np.abs(got - want16).max() <= 0.02 * rms + 1e-3, (np.abs(got - want16).max(), rms)
+    assert np.abs(got - want32).max() <= 0.04 * rms + 1e-3
+    net.close()
+
+
+@pytest.mark.parametrize("model,shape", [("body_25", (1, 368, 656)), ("body_25", (3, 112, 160)),
+                                         ("coco", (1, 184, 328)), ("hand", (2, 368, 368)), ("face", (1, 368, 368))])
+def test_openpose_models_within_tolerance(cuda, model, shape):
+    n, h, w = shape
+    proto, cm, ref = ref_net.build(model, 1234)
+    x = synth.frames_to_net_input(synth.frames(n, h, w, 21))
+    torch.set_num_threads(os.cpu_count() or 1)
+    want = ref.forward(x, keep=["net_output"])["net_output"]
+    net, got = _run(proto, cm, x)
+    assert got.shape == want.shape == (n, protogen.OUTPUT_CHANNELS[model], h // 8, w // 8)
+    err = float(np.abs(got - want).max())
+    assert err <= TOL_NET, "max-abs %.4f > %.4f (out rms %.3f)" % (err, TOL_NET, np.sqrt((want ** 2).mean()))
+    net.close()
+
+
+def test_reshape_device_input_and_repeatability(cuda):
+    proto, cm, ref = ref_net.build("body_25", 1234)
+    net = NetB200(proto, cm)
+    net.initializationOnThread()
+    outs = []
+    for (n, h, w) in [(1, 64, 96), (2, 48, 80), (1, 64, 96)]:
+        x = synth.frames_to_net_input(synth.frames(n, h, w, 5))
+        net.forwardPass(torch.from_numpy(x).to(cuda))          # device input
+        a = net.getOutputBlobArray().cpu().numpy().copy()
+        net.forwardPass(x)                                     # host input, graph replay
+        b = net.getOutputBlobArray().cpu().numpy().copy()
+        assert a.shape == (n, 78, h // 8, w // 8)
+        assert np.array_equal(a, b)                            # deterministic
+        want = ref.forward(x, keep=["net_output"])["net_output"]
+        assert np.abs(a - want).max() <= TOL_NET
+        outs.append(a)
+    assert np.array_equal(outs[0], outs[2])
+    net.close()
+
+
+def test_error_behaviour(tmp_path, cuda):
+    proto, cm, _ = ref_net.build("body_25", 1234)
+    with pytest.raises(Opb200Error, match="Prototxt file not found"):
+        NetB200(str(tmp_path / "missing.prototxt"), cm)
+    with pytest.raises(Opb200Error, match="Caffe trained model file not found"):
+        NetB200(proto, str(tmp_path / "missing.caffemodel"))
+    bad = NetB200(proto, cm, lastBlobName="no_such_blob")
+    with pytest.raises(Opb200Error, match="The output blob is a nullptr"):
+        bad.initializationOnThread()
+    net = NetB200(proto, cm)
+    net.initializationOnThread()
+    with pytest.raises(Opb200Error, match="must have 4 dimensions"):
+        net.forwardPass(np.zeros((1, 4, 16, 16), np.float32))
+    with pytest.raises(Opb200Error, match="cannot be empty"):
+        net.forwardPass(np.zeros((0, 3, 16, 16), np.float32))
+    net.close()
