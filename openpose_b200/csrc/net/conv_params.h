@@ -6,22 +6,28 @@
 namespace opb
 {
     constexpr int kConvMaxSegments = 4;   // a conv input is a (virtual) concat of <= 4 blob views
-    constexpr int kConvBlockM = 128;      // output pixels per tile = one TW x TH patch of one frame
+    constexpr int kConvTileW = 8;         // output tile = 8 x 16 pixels of one frame = 128 GEMM rows;
+    constexpr int kConvTileH = 16;        //   8 pixels = one 1024-byte swizzle group, so a filter-row shift is +1024 B
+    constexpr int kConvBlockM = kConvTileW * kConvTileH;
     constexpr int kConvBlockK = 64;       // channels per k-block = one 128-byte swizzled smem row
+    constexpr int kConvMaxKernel = 7;
 
     struct ConvParams
     {
-        CUtensorMap aMap[kConvMaxSegments];   // input views: dims (C, W, H, N) bf16, box (64, TW, TH, 1), SWIZZLE_128B
+        // input views: dims (C, W, H, N) bf16; box (64, 8, 16 + k - 1, 1) = the tile plus its vertical halo, SWIZZLE_128B
+        CUtensorMap aMap[kConvMaxSegments];
         CUtensorMap bMap;                     // weights: dims (Ktotal, CoutPad) bf16, box (64, BN), SWIZZLE_128B
-        CUtensorMap oMap;                     // output view: dims (Cout, W, H, N) bf16, box (32, TW, TH, 1), SWIZZLE_64B
+        CUtensorMap oMap;                     // output view: dims (Cout, W, H, N) bf16, box (32, 8, 16, 1), SWIZZLE_64B
         int segChunks[kConvMaxSegments];      // 64-channel chunks per segment (last chunk zero-filled by TMA)
         int nSeg;
         int chunksTotal;
-        int kh, kw, pad;
-        int H, W, N;                          // stride 1, "same" padding: output spatial == input spatial
-        int TW, TH, tilesX, tilesY;
+        int k, pad;                           // square odd kernel, "same" padding
+        int H, W, N;                          // stride 1: output spatial == input spatial
+        int tilesX, tilesY, numMTiles;        // numMTiles = N * tilesY * tilesX; a CTA works on PAIRS of M tiles
         int nTilesN;                          // Cout tiles of BN channels
         int cout;
+        int aTileBytes;                       // (16 + k - 1) * 1024
+        int aStages, bStages;                 // pipeline depths (A stage = 2 tiles x aTileBytes, B stage = BN x 128 B)
         const float* bias;                    // [nTilesN * BN], zero padded
         const float* slope;                   // negative-side slope per channel: 0 = ReLU, a_c = PReLU, 1 = identity
         float* out32;                         // optional fp32 NCHW copy of the output (net_output members)

@@ -6,14 +6,18 @@
 // concat copy (3rdparty/caffe/src/caffe/layers/cudnn_conv_layer.cu:21-37, relu_layer.cu:9, prelu_layer.cu:11-18,
 // concat_layer.cu:9) and on the CPU as im2col + sgemm (base_conv_layer.cpp:258-281).
 //
-// GEMM view: M = output pixels (tiles of 128 = TW x TH patch of one frame), N = Cout, K = taps x Cin.
-// No im2col buffer exists: for every filter tap the producer issues one 4-D TMA box load of the input patch
-// shifted by (kx - pad, ky - pad); TMA zero-fills out-of-image elements, which IS the conv's zero padding,
-// and zero-fills channels beyond a view's extent, which pads Cin to a multiple of 64 for free.
+// GEMM view: M = output pixels, N = Cout, K = Cin x taps. No im2col buffer exists anywhere.
+//   * M tile = 8 x 16 pixel patch of one frame (128 rows). Per 64-channel chunk and per filter COLUMN kx the
+//     producer loads ONE box (64 ch, 8 px, 16 + k - 1 rows) shifted by (kx - pad, -pad): the k filter ROWS ky are
+//     then just smem descriptor offsets of ky * 1024 B into that box (8 px x 128 B = one swizzle group), so an
+//     activation byte is fetched k times per layer instead of k*k times. TMA zero-fills out-of-image elements
+//     (= the conv's zero padding) and channels beyond a view's extent (= Cin padding to 64).
+//   * Each CTA works on a PAIR of M tiles against the same weight tile: every B (weight) stage feeds 8 MMAs
+//     (2 tiles x 4 k-steps), halving weight traffic per FLOP. 2 tiles x 2 accumulator stages x BN columns of TMEM.
+// The L2->SM operand stream, not the tensor pipe, bounds these layers (Cout <= 128): both measures cut bytes/FLOP.
 //
-// Roles (256 threads, persistent over tiles): warp 0 = TMA producer, warp 1 = MMA issuer (one thread),
+// Roles (256 threads, persistent over work items): warp 0 = TMA producer, warp 1 = MMA issuer (one thread),
 // warp 2 = TMEM allocator, warps 4-7 = epilogue (thread t <-> TMEM lane t <-> pixel t of the tile).
-// Two TMEM accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
 #include "../common.cuh"
 #include "conv_params.h"
 #include "sm100.cuh"
@@ -24,34 +28,55 @@ namespace opb
     using namespace sm100;
 
     constexpr int kConvThreads = 256;
-    constexpr int kABytes = kConvBlockM * kConvBlockK * 2;   // 16 KB
+    constexpr int kMaxAStages = 4, kMaxBStages = 8;
+    constexpr int kSmemLimit = 227 * 1024;
 
     template <int BN>
     struct ConvCfg
     {
         static constexpr int kBBytes = BN * kConvBlockK * 2;
-        static constexpr int kStageBytes = kABytes + kBBytes;
-        static constexpr int kStagingBytes = (BN / 32) * (kConvBlockM * 64);   // bf16 output tile, 32-channel pieces
-        static constexpr int kBudget = 222 * 1024;   // stages + staging; + 5 KB align/aux = 227 KB max dynamic smem
-        static constexpr int kStagesRaw = (kBudget - kStagingBytes) / kStageBytes;
-        static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
-        static constexpr int kAccStride = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));
-        static constexpr int kTmemCols = 2 * kAccStride;
-        static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align*/ + 4096 /*aux*/;
+        static constexpr int kStagingBytes = (BN / 32) * (kConvBlockM * 64);   // one bf16 output tile, 32-ch pieces
+        static constexpr int kAccStride = BN <= 32 ? 32 : (BN <= 64 ? 64 : 128);
+        static constexpr int kTmemCols = 4 * kAccStride;                       // 2 tiles x 2 accumulator stages
+        static_assert(BN <= 128 && BN % 16 == 0, "BN must be a multiple of 16, at most 128");
     };
 
     struct ConvAux   // barriers and small tables, placed after the pipeline buffers
     {
-        uint64_t full[8];
-        uint64_t empty[8];
-        uint64_t tmemFull[2];
-        uint64_t tmemEmpty[2];
+        uint64_t aFull[kMaxAStages], aEmpty[kMaxAStages];
+        uint64_t bFull[kMaxBStages], bEmpty[kMaxBStages];
+        uint64_t tmemFull[2], tmemEmpty[2];
         uint32_t tmemBase;
         uint32_t pad;
-        float bias[256];
-        float slope[256];
+        float bias[128];
+        float slope[128];
     };
-    static_assert(sizeof(ConvAux) <= 4096, "aux block too large");
+    constexpr int kAuxBytes = 2048;
+    static_assert(sizeof(ConvAux) <= kAuxBytes, "aux block too large");
+
+    struct TileCoord
+    {
+        int x0, y0, n;
+    };
+    // M tile index -> pixel origin. Indices past the end give a tile entirely outside the image: its loads are
+    // zero-filled and its stores clipped away by TMA (used for the odd tile of the last pair).
+    __device__ __forceinline__ TileCoord tileCoord(const ConvParams& p, int mt)
+    {
+        TileCoord c;
+        if (mt >= p.numMTiles)
+        {
+            c.x0 = 0;
+            c.y0 = p.tilesY * kConvTileH;
+            c.n = p.N - 1;
+            return c;
+        }
+        const int perFrame = p.tilesX * p.tilesY;
+        c.n = mt / perFrame;
+        const int r = mt - c.n * perFrame;
+        c.y0 = (r / p.tilesX) * kConvTileH;
+        c.x0 = (r % p.tilesX) * kConvTileW;
+        return c;
+    }
 
     template <int BN>
     __global__ void __launch_bounds__(kConvThreads, 1) convIgemmKernel(const __grid_constant__ ConvParams p)
@@ -59,16 +84,16 @@ namespace opb
         using Cfg = ConvCfg<BN>;
         extern __shared__ uint8_t smemRaw[];
         uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smemRaw) + 1023) & ~uintptr_t(1023));
-        uint8_t* sStage = smem;                                        // kStages x (A 16 KB | B)
-        uint8_t* sOut = smem + Cfg::kStages * Cfg::kStageBytes;        // staging for the TMA store
+        const int aStageBytes = 2 * p.aTileBytes;
+        uint8_t* sA = smem;                                         // aStages x (tile0 | tile1)
+        uint8_t* sB = sA + p.aStages * aStageBytes;                 // bStages x (BN x 128 B)
+        uint8_t* sOut = sB + p.bStages * Cfg::kBBytes;              // staging for the TMA store
         ConvAux* aux = reinterpret_cast<ConvAux*>(sOut + Cfg::kStagingBytes);
 
         const int warp = threadIdx.x >> 5;
         const int lane = threadIdx.x & 31;
-        const int tapsTotal = p.kh * p.kw;
-        const int numK = tapsTotal * p.chunksTotal;
-        const int tilesPerFrame = p.tilesX * p.tilesY;
-        const int numTiles = p.N * tilesPerFrame * p.nTilesN;
+        const int numPairs = (p.numMTiles + 1) >> 1;
+        const int numWork = numPairs * p.nTilesN;
 
         if (warp == 0 && lane == 0)
         {
@@ -79,10 +104,15 @@ namespace opb
         }
         if (warp == 1 && lane == 0)
         {
-            for (int i = 0; i < Cfg::kStages; ++i)
+            for (int i = 0; i < p.aStages; ++i)
             {
-                mbarInit(&aux->full[i], 1);
-                mbarInit(&aux->empty[i], 1);
+                mbarInit(&aux->aFull[i], 1);
+                mbarInit(&aux->aEmpty[i], 1);
+            }
+            for (int i = 0; i < p.bStages; ++i)
+            {
+                mbarInit(&aux->bFull[i], 1);
+                mbarInit(&aux->bEmpty[i], 1);
             }
             for (int i = 0; i < 2; ++i)
             {
@@ -103,35 +133,44 @@ namespace opb
             // ===================================== TMA producer ======================================
             if (lane == 0)
             {
-                int stage = 0;
-                uint32_t phase = 0;
-                for (int tile = blockIdx.x; tile < numTiles; tile += gridDim.x)
+                int as = 0, bs = 0;
+                uint32_t aPhase = 0, bPhase = 0;
+                for (int work = blockIdx.x; work < numWork; work += gridDim.x)
                 {
-                    const int nt = tile % p.nTilesN;
-                    const int m = tile / p.nTilesN;
-                    const int x0 = (m % p.tilesX) * p.TW;
-                    const int y0 = ((m / p.tilesX) % p.tilesY) * p.TH;
-                    const int n = m / tilesPerFrame;
-                    for (int tap = 0; tap < tapsTotal; ++tap)
-                    {
-                        const int ky = tap / p.kw, kx = tap - ky * p.kw;
-                        int kb = tap * p.chunksTotal;
-                        for (int s = 0; s < p.nSeg; ++s)
-                            for (int c = 0; c < p.segChunks[s]; ++c, ++kb)
+                    const int nt = work % p.nTilesN;
+                    const int pair = work / p.nTilesN;
+                    const TileCoord t0 = tileCoord(p, 2 * pair), t1 = tileCoord(p, 2 * pair + 1);
+                    int chunk = 0;
+                    for (int s = 0; s < p.nSeg; ++s)
+                        for (int c = 0; c < p.segChunks[s]; ++c, ++chunk)
+                            for (int kx = 0; kx < p.k; ++kx)
                             {
-                                mbarWait(&aux->empty[stage], phase ^ 1);
-                                uint8_t* sA = sStage + stage * Cfg::kStageBytes;
-                                mbarExpectTx(&aux->full[stage], Cfg::kStageBytes);
-                                tmaLoad4d(sA, &p.aMap[s], &aux->full[stage], c * kConvBlockK, x0 + kx - p.pad,
-                                          y0 + ky - p.pad, n);
-                                tmaLoad2d(sA + kABytes, &p.bMap, &aux->full[stage], kb * kConvBlockK, nt * BN);
-                                if (++stage == Cfg::kStages)
+                                mbarWait(&aux->aEmpty[as], aPhase ^ 1);
+                                uint8_t* dst = sA + as * aStageBytes;
+                                mbarExpectTx(&aux->aFull[as], aStageBytes);
+                                tmaLoad4d(dst, &p.aMap[s], &aux->aFull[as], c * kConvBlockK, t0.x0 + kx - p.pad,
+                                          t0.y0 - p.pad, t0.n);
+                                tmaLoad4d(dst + p.aTileBytes, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
+                                          t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
+                                if (++as == p.aStages)
                                 {
-                                    stage = 0;
-                                    phase ^= 1;
+                                    as = 0;
+                                    aPhase ^= 1;
+                                }
+                                const int kb0 = (chunk * p.k + kx) * p.k;
+                                for (int ky = 0; ky < p.k; ++ky)
+                                {
+                                    mbarWait(&aux->bEmpty[bs], bPhase ^ 1);
+                                    mbarExpectTx(&aux->bFull[bs], Cfg::kBBytes);
+                                    tmaLoad2d(sB + bs * Cfg::kBBytes, &p.bMap, &aux->bFull[bs], (kb0 + ky) * kConvBlockK,
+                                              nt * BN);
+                                    if (++bs == p.bStages)
+                                    {
+                                        bs = 0;
+                                        bPhase ^= 1;
+                                    }
                                 }
                             }
-                    }
                 }
             }
         }
@@ -141,33 +180,49 @@ namespace opb
             if (lane == 0)
             {
                 constexpr uint32_t idesc = instrDescBf16(kConvBlockM, BN);
-                int stage = 0;
-                uint32_t phase = 0;
-                int acc = 0;
-                uint32_t accPhase = 0;
-                for (int tile = blockIdx.x; tile < numTiles; tile += gridDim.x)
+                int as = 0, bs = 0, acc = 0;
+                uint32_t aPhase = 0, bPhase = 0, accPhase = 0;
+                const int numAx = p.chunksTotal * p.k;     // A stages consumed per work item
+                for (int work = blockIdx.x; work < numWork; work += gridDim.x)
                 {
                     mbarWait(&aux->tmemEmpty[acc], accPhase ^ 1);
                     tcFenceAfter();
-                    const uint32_t tmemD = tmemBase + acc * Cfg::kAccStride;
-                    for (int kb = 0; kb < numK; ++kb)
+                    const uint32_t tmemD0 = tmemBase + (acc * 2) * Cfg::kAccStride;
+                    const uint32_t tmemD1 = tmemD0 + Cfg::kAccStride;
+                    for (int ax = 0; ax < numAx; ++ax)
                     {
-                        mbarWait(&aux->full[stage], phase);
-                        tcFenceAfter();
-                        const uint32_t aAddr = smemAddr(sStage + stage * Cfg::kStageBytes);
-                        const uint64_t aDesc = smemDescSw128(aAddr);
-                        const uint64_t bDesc = smemDescSw128(aAddr + kABytes);
-#pragma unroll
-                        for (int k = 0; k < kConvBlockK / 16; ++k)   // 16 bf16 = 32 bytes per MMA along K
-                            mmaBf16(tmemD, aDesc + 2 * k, bDesc + 2 * k, idesc, (kb | k) != 0);
-                        mmaCommit(&aux->empty[stage]);                // smem slot free once these MMAs retire
-                        if (++stage == Cfg::kStages)
+                        mbarWait(&aux->aFull[as], aPhase);
+                        const uint32_t aAddr = smemAddr(sA + as * aStageBytes);
+                        for (int ky = 0; ky < p.k; ++ky)
                         {
-                            stage = 0;
-                            phase ^= 1;
+                            mbarWait(&aux->bFull[bs], bPhase);
+                            tcFenceAfter();
+                            // filter row ky = rows [8*ky, 8*ky + 128) of the halo box = +ky * 1024 bytes
+                            const uint64_t aDesc0 = smemDescSw128(aAddr + ky * 1024);
+                            const uint64_t aDesc1 = smemDescSw128(aAddr + p.aTileBytes + ky * 1024);
+                            const uint64_t bDesc = smemDescSw128(smemAddr(sB + bs * Cfg::kBBytes));
+                            const uint32_t first = (ax | ky) != 0;
+#pragma unroll
+                            for (int kk = 0; kk < kConvBlockK / 16; ++kk)   // 16 bf16 = 32 bytes per MMA along K
+                            {
+                                mmaBf16(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                mmaBf16(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                            }
+                            mmaCommit(&aux->bEmpty[bs]);          // weight slot free once these MMAs retire
+                            if (++bs == p.bStages)
+                            {
+                                bs = 0;
+                                bPhase ^= 1;
+                            }
+                        }
+                        mmaCommit(&aux->aEmpty[as]);              // activation slot free
+                        if (++as == p.aStages)
+                        {
+                            as = 0;
+                            aPhase ^= 1;
                         }
                     }
-                    mmaCommit(&aux->tmemFull[acc]);                   // accumulator complete -> epilogue
+                    mmaCommit(&aux->tmemFull[acc]);               // both accumulators complete -> epilogue
                     if (++acc == 2)
                     {
                         acc = 0;
@@ -181,23 +236,17 @@ namespace opb
             // ===================================== epilogue ==========================================
             const int t = threadIdx.x - 128;          // 0..127 = TMEM lane = pixel of the tile
             const int quad = warp & 3;                // warp (id % 4) may only touch lanes [32*quad, 32*quad+32)
-            const int tw = t % p.TW, th = t / p.TW;
+            const int tw = t % kConvTileW, th = t / kConvTileW;
             int acc = 0;
             uint32_t accPhase = 0;
             int lastNt = -1;
-            for (int tile = blockIdx.x; tile < numTiles; tile += gridDim.x)
+            for (int work = blockIdx.x; work < numWork; work += gridDim.x)
             {
-                const int nt = tile % p.nTilesN;
-                const int m = tile / p.nTilesN;
-                const int x0 = (m % p.tilesX) * p.TW;
-                const int y0 = ((m / p.tilesX) % p.tilesY) * p.TH;
-                const int n = m / tilesPerFrame;
-                // staging buffer and bias table are free once the previous tile's TMA store has read smem
-                if (t == 0)
-                    tmaStoreWaitRead0();
-                namedBarrier(1, 128);
+                const int nt = work % p.nTilesN;
+                const int pair = work / p.nTilesN;
                 if (nt != lastNt)
                 {
+                    namedBarrier(1, 128);             // everybody is done with the previous table
                     for (int i = t; i < BN; i += 128)
                     {
                         aux->bias[i] = __ldg(p.bias + nt * BN + i);
@@ -208,72 +257,89 @@ namespace opb
                 }
                 mbarWait(&aux->tmemFull[acc], accPhase);
                 tcFenceAfter();
-                const uint32_t taddr = tmemBase + acc * Cfg::kAccStride + ((uint32_t)(quad * 32) << 16);
-                const int x = x0 + tw, y = y0 + th;
-                const bool inImage = (x < p.W) && (y < p.H);
 #pragma unroll 1
-                for (int j = 0; j < BN / 32; ++j)
+                for (int j = 0; j < 2; ++j)
                 {
-                    uint32_t v[32];
-                    tmemLoad32(taddr + j * 32, v);
-                    tmemLoadWait();
-                    float f[32];
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
+                    const int mt = 2 * pair + j;
+                    if (mt >= p.numMTiles)
+                        break;                         // odd tile count: the last pair has no second tile
+                    const TileCoord tc = tileCoord(p, mt);
+                    // the staging buffer is free once the previous tile's TMA store has read it
+                    if (p.storeBf16)
                     {
-                        const float a = __uint_as_float(v[i]) + aux->bias[j * 32 + i];
-                        f[i] = a > 0.f ? a : a * aux->slope[j * 32 + i];
+                        if (t == 0)
+                            tmaStoreWaitRead0();
+                        namedBarrier(1, 128);
                     }
-                    if (p.out32 != nullptr && inImage)
+                    const uint32_t taddr =
+                        tmemBase + (acc * 2 + j) * Cfg::kAccStride + ((uint32_t)(quad * 32) << 16);
+                    const int x = tc.x0 + tw, y = tc.y0 + th;
+                    const bool inImage = (x < p.W) && (y < p.H);
+#pragma unroll 1
+                    for (int q = 0; q < BN / 32; ++q)
                     {
-                        const int cBase = nt * BN + j * 32;
-                        float* o = p.out32 + (((size_t)n * p.out32C + p.out32Off + cBase) * p.H + y) * p.W + x;
-                        const size_t plane = (size_t)p.H * p.W;
+                        uint32_t v[32];
+                        tmemLoad32(taddr + q * 32, v);
+                        tmemLoadWait();
+                        float f[32];
 #pragma unroll
                         for (int i = 0; i < 32; ++i)
-                            if (cBase + i < p.cout)
-                                o[i * plane] = f[i];
+                        {
+                            const float a = __uint_as_float(v[i]) + aux->bias[q * 32 + i];
+                            f[i] = a > 0.f ? a : a * aux->slope[q * 32 + i];
+                        }
+                        if (p.out32 != nullptr && inImage)
+                        {
+                            const int cBase = nt * BN + q * 32;
+                            float* o = p.out32 + (((size_t)tc.n * p.out32C + p.out32Off + cBase) * p.H + y) * p.W + x;
+                            const size_t plane = (size_t)p.H * p.W;
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (cBase + i < p.cout)
+                                    o[i * plane] = f[i];
+                        }
+                        if (p.storeBf16)
+                        {
+                            // row t of a 128 x 64-byte piece; 16-byte chunk c lands at c ^ ((t >> 1) & 3) (SWIZZLE_64B)
+                            uint8_t* row = sOut + q * (kConvBlockM * 64) + t * 64;
+                            const int sw = (t >> 1) & 3;
+#pragma unroll
+                            for (int c = 0; c < 4; ++c)
+                            {
+                                uint4 u;
+                                __nv_bfloat162 b0 = __floats2bfloat162_rn(f[c * 8 + 0], f[c * 8 + 1]);
+                                __nv_bfloat162 b1 = __floats2bfloat162_rn(f[c * 8 + 2], f[c * 8 + 3]);
+                                __nv_bfloat162 b2 = __floats2bfloat162_rn(f[c * 8 + 4], f[c * 8 + 5]);
+                                __nv_bfloat162 b3 = __floats2bfloat162_rn(f[c * 8 + 6], f[c * 8 + 7]);
+                                u.x = *reinterpret_cast<uint32_t*>(&b0);
+                                u.y = *reinterpret_cast<uint32_t*>(&b1);
+                                u.z = *reinterpret_cast<uint32_t*>(&b2);
+                                u.w = *reinterpret_cast<uint32_t*>(&b3);
+                                *reinterpret_cast<uint4*>(row + ((c ^ sw) << 4)) = u;
+                            }
+                        }
                     }
                     if (p.storeBf16)
                     {
-                        // row t of a 128 x 64-byte piece; 16-byte chunk c lands at c ^ ((t >> 1) & 3) (SWIZZLE_64B)
-                        uint8_t* row = sOut + j * (kConvBlockM * 64) + t * 64;
-                        const int sw = (t >> 1) & 3;
-#pragma unroll
-                        for (int c = 0; c < 4; ++c)
+                        fenceProxyAsyncShared();
+                        namedBarrier(1, 128);
+                        if (t == 0)
                         {
-                            uint4 q;
-                            __nv_bfloat162 b0 = __floats2bfloat162_rn(f[c * 8 + 0], f[c * 8 + 1]);
-                            __nv_bfloat162 b1 = __floats2bfloat162_rn(f[c * 8 + 2], f[c * 8 + 3]);
-                            __nv_bfloat162 b2 = __floats2bfloat162_rn(f[c * 8 + 4], f[c * 8 + 5]);
-                            __nv_bfloat162 b3 = __floats2bfloat162_rn(f[c * 8 + 6], f[c * 8 + 7]);
-                            q.x = *reinterpret_cast<uint32_t*>(&b0);
-                            q.y = *reinterpret_cast<uint32_t*>(&b1);
-                            q.z = *reinterpret_cast<uint32_t*>(&b2);
-                            q.w = *reinterpret_cast<uint32_t*>(&b3);
-                            *reinterpret_cast<uint4*>(row + ((c ^ sw) << 4)) = q;
+                            for (int q = 0; q < BN / 32; ++q)
+                                if (nt * BN + q * 32 < p.cout)
+                                    tmaStore4d(&p.oMap, sOut + q * (kConvBlockM * 64), nt * BN + q * 32, tc.x0, tc.y0,
+                                               tc.n);
+                            tmaStoreCommit();
                         }
                     }
                 }
-                // all TMEM reads of this thread are complete (wait::ld above): hand the accumulator back
+                // all TMEM reads of this thread are complete (wait::ld above): hand both accumulators back
                 tcFenceBefore();
                 mbarArrive(&aux->tmemEmpty[acc]);
                 if (++acc == 2)
                 {
                     acc = 0;
                     accPhase ^= 1;
-                }
-                if (p.storeBf16)
-                {
-                    fenceProxyAsyncShared();
-                    namedBarrier(1, 128);
-                    if (t == 0)
-                    {
-                        for (int j = 0; j < BN / 32; ++j)
-                            if (nt * BN + j * 32 < p.cout)
-                                tmaStore4d(&p.oMap, sOut + j * (kConvBlockM * 64), nt * BN + j * 32, x0, y0, n);
-                        tmaStoreCommit();
-                    }
                 }
             }
             if (t == 0)
@@ -285,39 +351,55 @@ namespace opb
             tmemFree<Cfg::kTmemCols>(tmemBase);
     }
 
+    // Pipeline depths for a given kernel size: 4 weight stages, as many activation stages as fit (2..4).
     template <int BN>
-    static opb200_status launchConvT(const ConvParams& p, int gridCap, cudaStream_t st)
+    static bool convSmemPlan(int k, int& aStages, int& bStages, int& smemBytes)
     {
         using Cfg = ConvCfg<BN>;
-        static bool configured = false;   // per process; the attribute is per function, set once per device below
-        static int configuredDev[64] = {0};
+        const int aStage = 2 * (kConvTileH + k - 1) * 1024;
+        bStages = BN <= 64 ? 6 : 4;
+        const int fixed = Cfg::kStagingBytes + kAuxBytes + 1024 /*alignment slack*/ + bStages * Cfg::kBBytes;
+        aStages = (kSmemLimit - fixed) / aStage;
+        if (aStages > kMaxAStages)
+            aStages = kMaxAStages;
+        smemBytes = fixed + aStages * aStage;
+        return aStages >= 2;
+    }
+
+    template <int BN>
+    static opb200_status launchConvT(ConvParams& p, int gridCap, cudaStream_t st)
+    {
+        int smemBytes = 0;
+        if (!convSmemPlan<BN>(p.k, p.aStages, p.bStages, smemBytes))
+            OPB_FAIL(OPB200_ERR_UNSUPPORTED, "conv: kernel size too large for the shared-memory pipeline");
+        p.aTileBytes = (kConvTileH + p.k - 1) * 1024;
+        static int configuredDev[64] = {0};   // attribute is per function per device; kSmemLimit covers every k
         int dev = 0;
         OPB_CUDA(cudaGetDevice(&dev));
-        if (!configured || !configuredDev[dev & 63])
+        if (!configuredDev[dev & 63])
         {
-            OPB_CUDA(cudaFuncSetAttribute(convIgemmKernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          Cfg::kSmemBytes));
-            configured = true;
+            OPB_CUDA(cudaFuncSetAttribute(convIgemmKernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
             configuredDev[dev & 63] = 1;
         }
-        const int numTiles = p.N * p.tilesX * p.tilesY * p.nTilesN;
-        int grid = numTiles < gridCap ? numTiles : gridCap;
+        const int numWork = ((p.numMTiles + 1) / 2) * p.nTilesN;
+        int grid = numWork < gridCap ? numWork : gridCap;
         if (grid < 1)
             grid = 1;
-        convIgemmKernel<BN><<<grid, kConvThreads, Cfg::kSmemBytes, st>>>(p);
+        convIgemmKernel<BN><<<grid, kConvThreads, smemBytes, st>>>(p);
         OPB_LAUNCH_CHECK();
         return OPB200_OK;
     }
 
-    opb200_status launchConv(const ConvParams& p, int bn, int gridCap, cudaStream_t st)
+    opb200_status launchConv(ConvParams& p, int bn, int gridCap, cudaStream_t st)
     {
+        if (p.k < 1 || p.k > kConvMaxKernel || p.k % 2 == 0)
+            OPB_FAIL(OPB200_ERR_UNSUPPORTED, "conv: kernel size must be odd and at most 7");
         switch (bn)
         {
         case 32: return launchConvT<32>(p, gridCap, st);
         case 64: return launchConvT<64>(p, gridCap, st);
         case 96: return launchConvT<96>(p, gridCap, st);
         case 128: return launchConvT<128>(p, gridCap, st);
-        case 256: return launchConvT<256>(p, gridCap, st);
         default: OPB_FAIL(OPB200_ERR_INVALID, "conv: unsupported BLOCK_N");
         }
     }

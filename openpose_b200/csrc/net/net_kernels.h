@@ -5,7 +5,7 @@
 
 namespace opb
 {
-    opb200_status launchConv(const ConvParams& p, int bn, int gridCap, cudaStream_t st);
+    opb200_status launchConv(ConvParams& p, int bn, int gridCap, cudaStream_t st);   // fills p's pipeline fields
     opb200_status launchInputPatch(void* dstBf16Nhwc, const float* srcNchw, int N, int C, int H, int W, int k, int pad,
                                    int dstC, cudaStream_t st);
     opb200_status launchMaxPool(void* dst, const void* src, int N, int C, int H, int W, int Ho, int Wo, int k,

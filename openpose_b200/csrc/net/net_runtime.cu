@@ -322,7 +322,6 @@ namespace opb
         };
 
         // ---- pass 3: ops ----------------------------------------------------------------------------
-        const bool bn256 = std::getenv("OPB200_CONV_BN256") != nullptr;
         std::vector<bool> consumed(def.layers.size(), false);
         for (size_t li = 0; li < def.layers.size(); ++li)
         {
@@ -392,8 +391,6 @@ namespace opb
                 if (op.in.size() > (size_t)kConvMaxSegments)
                     return planFail("layer " + L.name + ": more than 4 concatenated inputs");
                 op.bn = cout <= 32 ? 32 : (cout <= 64 ? 64 : (cout <= 96 ? 96 : 128));
-                if (bn256 && cout % 256 == 0)
-                    op.bn = 256;
                 op.nTilesN = (cout + op.bn - 1) / op.bn;
                 op.chunksTotal = 0;
                 for (size_t s = 0; s < op.in.size(); ++s)
@@ -421,13 +418,18 @@ namespace opb
                         for (int c = 0; c < op.in[s].C; ++c)
                         {
                             const int ci = segStart + c;
-                            for (int t = 0; t < taps; ++t)
-                            {
-                                const size_t col = ((size_t)t * op.chunksTotal + chunkStart) * kConvBlockK + c;
-                                for (int co = 0; co < cout; ++co)
-                                    op.hostW[(size_t)co * op.kTotal + col] =
-                                        __float2bfloat16(W.data[((size_t)co * cin + ci) * taps + t]);
-                            }
+                            // K order of the kernel: chunk-major, then filter column kx, then filter row ky
+                            const int chunk = chunkStart + c / kConvBlockK, lane = c % kConvBlockK;
+                            for (int ky = 0; ky < op.k; ++ky)
+                                for (int kx = 0; kx < op.k; ++kx)
+                                {
+                                    const size_t kb = ((size_t)chunk * op.k + kx) * op.k + ky;
+                                    const size_t col = kb * kConvBlockK + lane;
+                                    const int t = ky * op.k + kx;   // Caffe: W[co][ci][ky][kx]
+                                    for (int co = 0; co < cout; ++co)
+                                        op.hostW[(size_t)co * op.kTotal + col] =
+                                            __float2bfloat16(W.data[((size_t)co * cin + ci) * taps + t]);
+                                }
                         }
                         segStart += op.in[s].C;
                         chunkStart += op.segChunks[s];
@@ -616,25 +618,6 @@ namespace opb
     // ------------------------------------------------------------------------------------------------
     // reshape: level sizes, arena, tensor maps (reference: reshapeNetCaffe, netCaffe.cpp:105-122)
     // ------------------------------------------------------------------------------------------------
-    static void chooseTile(int W, int H, int& TW, int& TH)
-    {
-        double best = -1;
-        TW = 8;
-        TH = 16;
-        for (int tw = 128; tw >= 1; tw >>= 1)   // prefer wide tiles on ties
-        {
-            const int th = kConvBlockM / tw;
-            const double tiles = (double)((W + tw - 1) / tw) * ((H + th - 1) / th);
-            const double eff = (double)W * H / (tiles * kConvBlockM);
-            if (eff > best + 1e-9)
-            {
-                best = eff;
-                TW = tw;
-                TH = th;
-            }
-        }
-    }
-
     static opb200_status reshapeNet(Net& net, int N, int H, int W)
     {
         if (net.graphExec)
@@ -693,13 +676,13 @@ namespace opb
             const int h = net.lvH[op.level], w = net.lvW[op.level];
             ConvParams& p = op.cp;
             std::memset(&p, 0, sizeof(p));
-            chooseTile(w, h, p.TW, p.TH);
-            p.tilesX = (w + p.TW - 1) / p.TW;
-            p.tilesY = (h + p.TH - 1) / p.TH;
+            p.tilesX = (w + kConvTileW - 1) / kConvTileW;
+            p.tilesY = (h + kConvTileH - 1) / kConvTileH;
+            p.numMTiles = N * p.tilesX * p.tilesY;
             p.H = h;
             p.W = w;
             p.N = N;
-            p.kh = p.kw = op.k;
+            p.k = op.k;
             p.pad = op.pad;
             p.nSeg = (int)op.in.size();
             p.chunksTotal = op.chunksTotal;
@@ -715,15 +698,16 @@ namespace opb
             {
                 p.segChunks[s] = op.segChunks[s];
                 const opb200_status st = makeActivationMap(&p.aMap[s], viewPtr(op.in[s]), op.in[s].C, w, h, N,
-                                                           net.buffers[op.in[s].buf].C, kConvBlockK, p.TW, p.TH, true);
+                                                           net.buffers[op.in[s].buf].C, kConvBlockK, kConvTileW,
+                                                           kConvTileH + op.k - 1, true);
                 if (st != OPB200_OK)
                     return st;
             }
             opb200_status st = makeWeightMap(&p.bMap, op.dW, op.kTotal, op.nTilesN * op.bn, op.bn);
             if (st != OPB200_OK)
                 return st;
-            st = makeActivationMap(&p.oMap, viewPtr(op.out), op.out.C, w, h, N, net.buffers[op.out.buf].C, 32, p.TW,
-                                   p.TH, false);
+            st = makeActivationMap(&p.oMap, viewPtr(op.out), op.out.C, w, h, N, net.buffers[op.out.buf].C, 32,
+                                   kConvTileW, kConvTileH, false);
             if (st != OPB200_OK)
                 return st;
             net.flopsPerForward += op.flopsPerPixel * (double)N * h * w;
