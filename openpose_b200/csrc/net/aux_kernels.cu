@@ -139,3 +139,162 @@ namespace opb
         return OPB200_OK;
     }
 }
+
+// ----------------------------------------------------------------------------------------------------
+// First layer (Cin*k*k <= 32, Cout <= 64): fp32 NCHW input -> conv + bias + activation -> bf16 NHWC, one pass.
+// 0.3 % of the net's FLOPs but, as a padded K=64 GEMM behind an im2col buffer, 10 % of its time: here the
+// 27-element patches are gathered straight into mma.sync (m16n8k16, bf16 in / fp32 accumulate) A fragments, so the
+// layer costs one read of the input and one coalesced write of its output (HBM bound: 12*H*W + 2*Cout*H*W bytes).
+// Each warp owns 32 consecutive pixels (two m16 tiles) x all Cout channels; weights live in registers as B fragments.
+// ----------------------------------------------------------------------------------------------------
+namespace opb
+{
+    __device__ __forceinline__ void mmaSyncBf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1)
+    {
+        asm volatile(
+            "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+            : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+    }
+    __device__ __forceinline__ uint32_t packBf16(float lo, float hi)
+    {
+        __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+        return *reinterpret_cast<uint32_t*>(&v);
+    }
+
+    constexpr int kFirstWarps = 8;
+    constexpr int kFirstPitch = 144;   // bytes per staged pixel row (128 + 16: conflict-free 16-byte reads)
+
+    __global__ void __launch_bounds__(kFirstWarps * 32) firstConvKernel(
+        __nv_bfloat16* __restrict__ dst, const float* __restrict__ src, const uint32_t* __restrict__ wfrag,
+        const float* __restrict__ bias, const float* __restrict__ slope, int N, int C, int H, int W, int k, int pad,
+        int cout, int dstStride)
+    {
+        __shared__ __align__(16) uint8_t stage[kFirstWarps][32 * kFirstPitch];
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        const int g = lane >> 2, q = lane & 3;
+        const int kk = k * k, K = C * kk;
+        const int nTiles = cout >> 3;
+        // B fragments of all (n-tile, k-step) pairs: 32 registers
+        uint32_t wb[8][2][2];
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+            for (int s = 0; s < 2; ++s)
+            {
+                const uint2 v = nt < nTiles ? __ldg(reinterpret_cast<const uint2*>(wfrag) + (nt * 2 + s) * 32 + lane)
+                                            : make_uint2(0u, 0u);
+                wb[nt][s][0] = v.x;
+                wb[nt][s][1] = v.y;
+            }
+        // the 8 patch elements this thread gathers per pixel: j = 16*s + 2*q + {0,1,8,9}
+        int jOff[8], jDy[8], jDx[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+        {
+            const int j = 16 * (e >> 2) + 2 * q + (e & 1) + ((e >> 1) & 1) * 8;
+            if (j < K)
+            {
+                const int c = j / kk, r = j - c * kk;
+                jOff[e] = c * H * W;
+                jDy[e] = r / k - pad;
+                jDx[e] = r % k - pad;
+            }
+            else
+            {
+                jOff[e] = -1;
+                jDy[e] = jDx[e] = 0;
+            }
+        }
+        const long long total = (long long)N * H * W;
+        const long long step = (long long)gridDim.x * kFirstWarps * 32;
+        for (long long p0 = ((long long)blockIdx.x * kFirstWarps + warp) * 32; p0 < total; p0 += step)
+        {
+            uint32_t a[2][2][4];   // [m tile][k step][fragment register]
+#pragma unroll
+            for (int t = 0; t < 2; ++t)
+#pragma unroll
+                for (int hrow = 0; hrow < 2; ++hrow)
+                {
+                    const long long p = p0 + t * 16 + hrow * 8 + g;
+                    float v[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e)
+                        v[e] = 0.f;
+                    if (p < total)
+                    {
+                        const int x = (int)(p % W);
+                        const int y = (int)((p / W) % H);
+                        const long long base = (p / ((long long)W * H)) * (long long)C * H * W;
+#pragma unroll
+                        for (int e = 0; e < 8; ++e)
+                        {
+                            const int yy = y + jDy[e], xx = x + jDx[e];
+                            if (jOff[e] >= 0 && yy >= 0 && yy < H && xx >= 0 && xx < W)
+                                v[e] = __ldg(src + base + jOff[e] + (long long)yy * W + xx);
+                        }
+                    }
+                    // e = 4*s + 2*hi8 + lo : registers a0 (row g, k lo), a1 (row g+8), a2 (row g, k+8), a3 (row g+8, k+8)
+#pragma unroll
+                    for (int s = 0; s < 2; ++s)
+                    {
+                        a[t][s][hrow] = packBf16(v[4 * s + 0], v[4 * s + 1]);
+                        a[t][s][2 + hrow] = packBf16(v[4 * s + 2], v[4 * s + 3]);
+                    }
+                }
+            uint8_t* st = stage[warp];
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt)
+            {
+                if (nt >= nTiles)
+                    break;
+                const float2 b2 = __ldg(reinterpret_cast<const float2*>(bias) + nt * 4 + q);
+                const float2 s2 = __ldg(reinterpret_cast<const float2*>(slope) + nt * 4 + q);
+#pragma unroll
+                for (int t = 0; t < 2; ++t)
+                {
+                    float c[4] = {0.f, 0.f, 0.f, 0.f};
+                    mmaSyncBf16(c, a[t][0], wb[nt][0][0], wb[nt][0][1]);
+                    mmaSyncBf16(c, a[t][1], wb[nt][1][0], wb[nt][1][1]);
+                    float o[4];
+                    o[0] = c[0] + b2.x;
+                    o[1] = c[1] + b2.y;
+                    o[2] = c[2] + b2.x;
+                    o[3] = c[3] + b2.y;
+                    o[0] = o[0] > 0.f ? o[0] : o[0] * s2.x;
+                    o[1] = o[1] > 0.f ? o[1] : o[1] * s2.y;
+                    o[2] = o[2] > 0.f ? o[2] : o[2] * s2.x;
+                    o[3] = o[3] > 0.f ? o[3] : o[3] * s2.y;
+                    *reinterpret_cast<uint32_t*>(st + (t * 16 + g) * kFirstPitch + nt * 16 + q * 4) = packBf16(o[0], o[1]);
+                    *reinterpret_cast<uint32_t*>(st + (t * 16 + g + 8) * kFirstPitch + nt * 16 + q * 4) = packBf16(o[2], o[3]);
+                }
+            }
+            __syncwarp();
+            // 32 pixels x nTiles 16-byte chunks, written so that a pixel's channels are contiguous in global memory
+            const int chunks = 32 * nTiles;
+            for (int i = lane; i < chunks; i += 32)
+            {
+                const int px = i / nTiles, ch = i - px * nTiles;
+                if (p0 + px < total)
+                    *reinterpret_cast<uint4*>(dst + (p0 + px) * dstStride + ch * 8) =
+                        *reinterpret_cast<const uint4*>(st + px * kFirstPitch + ch * 16);
+            }
+            __syncwarp();
+        }
+    }
+
+    opb200_status launchFirstConv(void* dst, const float* src, const uint32_t* wfrag, const float* bias,
+                                  const float* slope, int N, int C, int H, int W, int k, int pad, int cout,
+                                  int dstStride, cudaStream_t st)
+    {
+        OPB_REQUIRE(C * k * k <= 32 && cout % 8 == 0 && cout <= 64 && dstStride % 8 == 0,
+                    "first conv: needs Cin*k*k <= 32 and Cout a multiple of 8, at most 64");
+        const long long total = (long long)N * H * W;
+        const long long want = (total + kFirstWarps * 32 - 1) / (kFirstWarps * 32);
+        const int blocks = (int)(want < 148 * 8 ? want : 148 * 8);
+        firstConvKernel<<<blocks > 0 ? blocks : 1, kFirstWarps * 32, 0, st>>>(
+            static_cast<__nv_bfloat16*>(dst), src, wfrag, bias, slope, N, C, H, W, k, pad, cout, dstStride);
+        OPB_LAUNCH_CHECK();
+        return OPB200_OK;
+    }
+}

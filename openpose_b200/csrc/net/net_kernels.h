@@ -8,6 +8,10 @@ namespace opb
     opb200_status launchConv(ConvParams& p, int bn, int gridCap, cudaStream_t st);   // fills p's pipeline fields
     opb200_status launchInputPatch(void* dstBf16Nhwc, const float* srcNchw, int N, int C, int H, int W, int k, int pad,
                                    int dstC, cudaStream_t st);
+    // First layer straight from the fp32 NCHW input (Cin*k*k <= 32, Cout <= 64): mma.sync, fused bias/activation.
+    opb200_status launchFirstConv(void* dstBf16Nhwc, const float* srcNchw, const uint32_t* wfrag, const float* bias,
+                                  const float* slope, int N, int C, int H, int W, int k, int pad, int cout,
+                                  int dstStride, cudaStream_t st);
     opb200_status launchMaxPool(void* dst, const void* src, int N, int C, int H, int W, int Ho, int Wo, int k,
                                 int stride, int srcStride, int dstStride, cudaStream_t st);
     opb200_status launchNhwcToNchw(float* dst, const void* src, int N, int C, int H, int W, int srcStride, int dstC,

@@ -108,7 +108,8 @@ namespace opb
         OP_PATCH,
         OP_CONV,
         OP_POOL,
-        OP_CONVERT
+        OP_CONVERT,
+        OP_FIRSTCONV   // first layer straight from the fp32 NCHW input (mma.sync kernel in aux_kernels.cu)
     };
     struct Op
     {
@@ -122,6 +123,7 @@ namespace opb
         int segChunks[kConvMaxSegments] = {0, 0, 0, 0};
         std::vector<__nv_bfloat16> hostW;   // [nTilesN*bn][kTotal]
         std::vector<float> hostBias, hostSlope;
+        std::vector<uint32_t> hostFrag;     // OP_FIRSTCONV: mma.sync B fragments [n-tile][k-step][lane][2]
         __nv_bfloat16* dW = nullptr;
         float *dBias = nullptr, *dSlope = nullptr;
         int out32Off = -1;
@@ -364,7 +366,16 @@ namespace opb
                 op.cout = cout;
                 op.flopsPerPixel = 2.0 * cout * cin * k * k;
                 bool patch = false;
-                if (src.isInput)
+                const bool direct = src.isInput && cin * k * k <= 32 && cout <= 64 && cout % 8 == 0 &&
+                                    std::getenv("OPB200_NO_FIRSTCONV") == nullptr;
+                if (direct)
+                {
+                    op.kind = OP_FIRSTCONV;
+                    op.inC = cin;
+                    op.k = k;
+                    op.pad = L.pad;
+                }
+                else if (src.isInput)
                 {
                     // first layer: fp32 NCHW input -> bf16 patch tensor; conv becomes 1x1 when Cin*k*k <= 64
                     patch = cin * k * k <= kConvBlockK;
@@ -404,7 +415,32 @@ namespace opb
                 op.hostW.assign((size_t)rows * op.kTotal, __float2bfloat16(0.f));
                 op.hostBias.assign(rows, 0.f);
                 op.hostSlope.assign(rows, 1.f);   // identity unless an activation layer follows
-                if (patch)
+                if (direct)
+                {
+                    // B fragment of mma.m16n8k16 (16x8, "col"): lane (g = lane/4, q = lane%4) holds
+                    // {B[2q][g], B[2q+1][g]} and {B[2q+8][g], B[2q+9][g]}, B[kidx][n] = W[n][kidx], kidx = c*k*k + ky*k + kx
+                    const int K = cin * k * k;
+                    auto wAt = [&](int n, int j) { return (n < cout && j < K) ? W.data[(size_t)n * K + j] : 0.f; };
+                    auto pack = [&](float lo, float hi) {
+                        const __nv_bfloat16 a = __float2bfloat16(lo), b = __float2bfloat16(hi);
+                        uint16_t ua, ub;
+                        std::memcpy(&ua, &a, 2);
+                        std::memcpy(&ub, &b, 2);
+                        return (uint32_t)ua | ((uint32_t)ub << 16);
+                    };
+                    op.hostFrag.assign(8 * 2 * 32 * 2, 0u);
+                    for (int nt = 0; nt < 8; ++nt)
+                        for (int s2 = 0; s2 < 2; ++s2)
+                            for (int lane = 0; lane < 32; ++lane)
+                            {
+                                const int g = lane >> 2, q = lane & 3, n = nt * 8 + g, j = 16 * s2 + 2 * q;
+                                uint32_t* f = &op.hostFrag[((size_t)(nt * 2 + s2) * 32 + lane) * 2];
+                                f[0] = pack(wAt(n, j), wAt(n, j + 1));
+                                f[1] = pack(wAt(n, j + 8), wAt(n, j + 9));
+                            }
+                    op.hostW.clear();
+                }
+                else if (patch)
                 {
                     for (int co = 0; co < cout; ++co)
                         for (int j = 0; j < cin * k * k; ++j)
@@ -601,12 +637,22 @@ namespace opb
     {
         for (auto& op : net.ops)
         {
-            if (op.kind != OP_CONV)
+            if (op.kind != OP_CONV && op.kind != OP_FIRSTCONV)
                 continue;
-            OPB_CUDA(cudaMalloc(&op.dW, op.hostW.size() * sizeof(__nv_bfloat16)));
+            if (op.kind == OP_FIRSTCONV)
+            {
+                OPB_CUDA(cudaMalloc(&op.dW, op.hostFrag.size() * sizeof(uint32_t)));
+                OPB_CUDA(cudaMemcpy(op.dW, op.hostFrag.data(), op.hostFrag.size() * sizeof(uint32_t),
+                                    cudaMemcpyHostToDevice));
+            }
+            else
+            {
+                OPB_CUDA(cudaMalloc(&op.dW, op.hostW.size() * sizeof(__nv_bfloat16)));
+                OPB_CUDA(cudaMemcpy(op.dW, op.hostW.data(), op.hostW.size() * sizeof(__nv_bfloat16),
+                                    cudaMemcpyHostToDevice));
+            }
             OPB_CUDA(cudaMalloc(&op.dBias, op.hostBias.size() * sizeof(float)));
             OPB_CUDA(cudaMalloc(&op.dSlope, op.hostSlope.size() * sizeof(float)));
-            OPB_CUDA(cudaMemcpy(op.dW, op.hostW.data(), op.hostW.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
             OPB_CUDA(cudaMemcpy(op.dBias, op.hostBias.data(), op.hostBias.size() * sizeof(float), cudaMemcpyHostToDevice));
             OPB_CUDA(cudaMemcpy(op.dSlope, op.hostSlope.data(), op.hostSlope.size() * sizeof(float),
                                 cudaMemcpyHostToDevice));
@@ -671,6 +717,8 @@ namespace opb
         };
         for (auto& op : net.ops)
         {
+            if (op.kind == OP_FIRSTCONV)
+                net.flopsPerForward += op.flopsPerPixel * (double)N * net.lvH[op.level] * net.lvW[op.level];
             if (op.kind != OP_CONV)
                 continue;
             const int h = net.lvH[op.level], w = net.lvW[op.level];
@@ -741,6 +789,11 @@ namespace opb
                                      net.buffers[op.out.buf].C, st);
                 break;
             case OP_CONV: s = launchConv(op.cp, op.bn, net.gridCap, st); break;
+            case OP_FIRSTCONV:
+                s = launchFirstConv(viewPtr(op.out), net.dInput, reinterpret_cast<const uint32_t*>(op.dW), op.dBias,
+                                    op.dSlope, net.N, op.inC, h, w, op.k, op.pad, op.cout, net.buffers[op.out.buf].C,
+                                    st);
+                break;
             case OP_POOL:
                 s = launchMaxPool(viewPtr(op.out), viewPtr(op.in[0]), net.N, op.in[0].C, h, w, net.lvH[op.outLevel],
                                   net.lvW[op.outLevel], op.k, op.stride, net.buffers[op.in[0].buf].C,
@@ -935,7 +988,7 @@ extern "C" opb200_status opb200_net_info(opb200_net* n, opb200_net_info_t* info)
     Net& net = n->h.net;
     int convs = 0;
     for (const auto& op : net.ops)
-        convs += op.kind == OP_CONV;
+        convs += (op.kind == OP_CONV || op.kind == OP_FIRSTCONV);
     info->conv_layers = convs;
     info->kernel_launches_per_forward = (int)net.ops.size();
     info->flops_per_forward = net.flopsPerForward;
@@ -1019,7 +1072,7 @@ extern "C" opb200_status opb200_net_describe(const char* prototxt, const char* c
         return s;
     std::string out;
     char line[1024];
-    static const char* kinds[] = {"patch", "conv", "pool", "convert"};
+    static const char* kinds[] = {"patch", "conv", "pool", "convert", "conv"};
     for (const auto& op : net.ops)
     {
         std::string segs;

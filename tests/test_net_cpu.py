@@ -107,7 +107,7 @@ def test_cpp_planner_covers_every_layer(model):
         kv = dict(t.split("=", 1) for t in c[2:])
         assert int(kv["cout"]) == L.params["num_output"] == blobs[L.name][0].shape[0]
         assert int(kv["cin"]) == blobs[L.name][0].shape[1]
-        segs = [tuple(int(v) for v in s.split(":")) for s in kv["segs"].strip("[]").split(",")]
+        segs = [tuple(int(v) for v in s.split(":")) for s in kv["segs"].strip("[]").split(",") if s]
         if L.bottoms[0] != "image":
             assert sum(s[2] for s in segs) == int(kv["cin"])          # concat segments cover the input channels
         assert all(s[1] % 8 == 0 for s in segs)                      # 16-byte aligned TMA bases
