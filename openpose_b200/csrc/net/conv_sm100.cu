@@ -22,6 +22,7 @@
 #include "conv_params.h"
 #include "sm100.cuh"
 #include <cuda_bf16.h>
+#include <cstdlib>
 
 namespace opb
 {
@@ -90,6 +91,9 @@ namespace opb
         uint8_t* sOut = sB + p.bStages * Cfg::kBBytes;              // staging for the TMA store
         ConvAux* aux = reinterpret_cast<ConvAux*>(sOut + Cfg::kStagingBytes);
 
+        // Programmatic dependent launch: let the next layer's CTAs start their prologue on SMs this grid has
+        // already vacated; they block in griddepcontrol.wait (below) until this grid has completed and flushed.
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         const int warp = threadIdx.x >> 5;
         const int lane = threadIdx.x & 31;
         const int numPairs = (p.numMTiles + 1) >> 1;
@@ -127,6 +131,9 @@ namespace opb
         __syncthreads();
         tcFenceAfter();
         const uint32_t tmemBase = aux->tmemBase;
+        // everything above touched only kernel parameters, smem and TMEM; from here on we read the previous
+        // layer's output and overwrite buffers it may still be reading
+        asm volatile("griddepcontrol.wait;" ::: "memory");
 
         if (warp == 0)
         {
@@ -385,7 +392,18 @@ namespace opb
         int grid = numWork < gridCap ? numWork : gridCap;
         if (grid < 1)
             grid = 1;
-        convIgemmKernel<BN><<<grid, kConvThreads, smemBytes, st>>>(p);
+        static const bool usePdl = std::getenv("OPB200_NO_PDL") == nullptr;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(kConvThreads);
+        cfg.dynamicSmemBytes = smemBytes;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = usePdl ? 1 : 0;
+        OPB_CUDA(cudaLaunchKernelEx(&cfg, convIgemmKernel<BN>, p));
         OPB_LAUNCH_CHECK();
         return OPB200_OK;
     }
