@@ -123,58 +123,73 @@ namespace opb
         int* myList = warpLists + warp * a.maxPeaks;
         int count = 0;                                   // warp-uniform
 
-        for (int base = segBegin; base < segEnd && count < a.maxPeaks; base += kChunk)
+        // kUnroll independent 128-bit loads per lane are issued before any of them is examined: the peak count
+        // that steers the loop depends on the loaded values, so without this only one load per warp is in flight
+        // and the scan is latency bound (measured 1.2 TB/s); sub-chunks are then processed in raster order.
+        constexpr int kUnroll = 4;
+        for (int base = segBegin; base < segEnd && count < a.maxPeaks; base += kChunk * kUnroll)
         {
-            const int pix = base + lane * 4;
-            float v[4];
-            if (VEC)
+            float v[kUnroll][4];
+#pragma unroll
+            for (int u = 0; u < kUnroll; u++)
             {
-                float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (pix < segEnd)
-                    q = __ldg(reinterpret_cast<const float4*>(plane + pix));
-                v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+                const int pix = base + u * kChunk + lane * 4;
+                if (VEC)
+                {
+                    float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (pix < segEnd)
+                        q = __ldg(reinterpret_cast<const float4*>(plane + pix));
+                    v[u][0] = q.x; v[u][1] = q.y; v[u][2] = q.z; v[u][3] = q.w;
+                }
+                else
+                {
+#pragma unroll
+                    for (int e = 0; e < 4; e++)
+                        v[u][e] = (pix + e < segEnd) ? __ldg(plane + pix + e) : 0.f;
+                }
             }
-            else
+#pragma unroll
+            for (int u = 0; u < kUnroll; u++)
             {
+                const int pix = base + u * kChunk + lane * 4;
+                unsigned mask = 0;
 #pragma unroll
                 for (int e = 0; e < 4; e++)
-                    v[e] = (pix + e < segEnd) ? __ldg(plane + pix + e) : 0.f;
-            }
-            unsigned mask = 0;
-#pragma unroll
-            for (int e = 0; e < 4; e++)
-            {
-                // thr >= 0, so the zero fill of out-of-range lanes can never pass.
-                if (v[e] > a.thr && pix + e < segEnd)
                 {
-                    const int y = (pix + e) / a.w, x = (pix + e) - y * a.w;
-                    const bool pk = MODE == OPB200_SEMANTICS_CPU ? isPeakCpu(plane, a.w, a.h, a.thr, x, y, v[e])
-                                                                 : isPeakCuda(plane, a.w, a.h, x, y, v[e]);
-                    mask |= pk ? (1u << e) : 0u;
+                    // thr >= 0, so the zero fill of out-of-range lanes can never pass.
+                    if (v[u][e] > a.thr && pix + e < segEnd)
+                    {
+                        const int y = (pix + e) / a.w, x = (pix + e) - y * a.w;
+                        const bool pk = MODE == OPB200_SEMANTICS_CPU
+                                            ? isPeakCpu(plane, a.w, a.h, a.thr, x, y, v[u][e])
+                                            : isPeakCuda(plane, a.w, a.h, x, y, v[u][e]);
+                        mask |= pk ? (1u << e) : 0u;
+                    }
+                }
+                if (__ballot_sync(0xffffffffu, mask != 0) != 0)
+                {
+                    // raster-order compaction: lane-major, then element order inside the lane
+                    const int mine = __popc(mask);
+                    int incl = mine;
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1)
+                    {
+                        const int t = __shfl_up_sync(0xffffffffu, incl, d);
+                        if (lane >= d)
+                            incl += t;
+                    }
+                    int slot = count + incl - mine;
+#pragma unroll
+                    for (int e = 0; e < 4; e++)
+                        if (mask & (1u << e))
+                        {
+                            if (slot < a.maxPeaks)
+                                myList[slot] = pix + e;
+                            slot++;
+                        }
+                    count += __shfl_sync(0xffffffffu, incl, 31);
                 }
             }
-            if (__ballot_sync(0xffffffffu, mask != 0) == 0)
-                continue;
-            // raster-order compaction: lane-major, then element order inside the lane
-            const int mine = __popc(mask);
-            int incl = mine;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1)
-            {
-                const int t = __shfl_up_sync(0xffffffffu, incl, d);
-                if (lane >= d)
-                    incl += t;
-            }
-            int slot = count + incl - mine;
-#pragma unroll
-            for (int e = 0; e < 4; e++)
-                if (mask & (1u << e))
-                {
-                    if (slot < a.maxPeaks)
-                        myList[slot] = pix + e;
-                    slot++;
-                }
-            count += __shfl_sync(0xffffffffu, incl, 31);
         }
         if (lane == 0)
             warpCounts[warp] = min(count, a.maxPeaks);

@@ -78,15 +78,36 @@ namespace opb
             srcRows[i] = __ldg(sp + (size_t)rbase * ws + i);
         __syncthreads();
 
-        // x-pass: tmp[j][x] = cubic along x of source row rbase+j
-        for (int i = threadIdx.x; i < nrows * wt; i += kR8Threads)
+        // x-pass: tmp[j][x] = cubic along x of source row rbase+j. The 8 outputs x = 8g+4 .. 8g+11 share
+        // floor(xs) = g and therefore their 4 taps: the polynomial coefficients are computed once per (row, g) and
+        // evaluated 8 times (same operations in the same order as cubic1d, so the result is bit-identical).
+        const int groupsX = ws + 1;                      // g = -1 .. ws-1
+        for (int i = threadIdx.x; i < nrows * groupsX; i += kR8Threads)
         {
-            const int j = i / wt, x = i - j * wt;
-            int xi[4];
-            float dx;
-            taps(xi, dx, srcCoord8(x), ws);
+            const int j = i / groupsX, g = i - j * groupsX - 1;
+            const int x1 = min(ws - 1, max(0, g));
+            const int x0 = max(0, x1 - 1), x2 = min(ws - 1, x1 + 1), x3 = min(ws - 1, x2 + 1);
             const float* r = srcRows + j * ws;
-            tmp[j * wt + x] = cubic1d(r[xi[0]], r[xi[1]], r[xi[2]], r[xi[3]], dx);
+            const float v0 = r[x0], v1 = r[x1], v2 = r[x2], v3 = r[x3];
+            const float A = cubicA(v0, v1, v2, v3), B = cubicB(v0, v1, v2, v3), C = cubicC(v0, v2);
+            const float fx1 = (float)x1;
+            const int xb = 8 * g + 4;
+            float* t = tmp + j * wt;
+            if (xb >= 0 && xb + 8 <= wt)
+            {
+                float o[8];
+#pragma unroll
+                for (int e = 0; e < 8; e++)
+                    o[e] = cubicEval(A, B, C, v1, sub(srcCoord8(xb + e), fx1));
+                *reinterpret_cast<float4*>(t + xb) = make_float4(o[0], o[1], o[2], o[3]);
+                *reinterpret_cast<float4*>(t + xb + 4) = make_float4(o[4], o[5], o[6], o[7]);
+            }
+            else
+            {
+                const int xe = min(wt, xb + 8);
+                for (int x = max(0, xb); x < xe; x++)
+                    t[x] = cubicEval(A, B, C, v1, sub(srcCoord8(x), fx1));
+            }
         }
         __syncthreads();
 
