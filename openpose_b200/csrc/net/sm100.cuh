@@ -78,6 +78,13 @@ namespace sm100
             "r"(c3)
             : "memory");
     }
+    // 1-D bulk copy global -> shared (no tensor map): size and both addresses multiples of 16 bytes.
+    __device__ __forceinline__ void bulkLoad1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
+    {
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smemAddr(dst)), "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(smemAddr(bar))
+                     : "memory");
+    }
     __device__ __forceinline__ void tmaStore4d(const CUtensorMap* m, const void* src, int c0, int c1, int c2, int c3)
     {
         asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
