@@ -191,9 +191,18 @@ def dist_init(n_gpus: int):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:
         import torch.distributed as dist
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        backend = os.environ.get("OPB200_DIST_BACKEND", "nccl")   # "gloo": the CPU tests of this plumbing
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        else:
+            dist.init_process_group(backend)
     return rank, world, local
+
+
+def whole_job_rate(units_local: float, seconds_local: float, world: int, device) -> float:
+    """Units all ranks processed / the slowest rank's time (frame sharding: ranks never exchange data)."""
+    return sum_over_ranks(units_local, world, device) / max_over_ranks(seconds_local, world, device)
 
 
 def barrier(world):

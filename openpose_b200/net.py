@@ -133,7 +133,7 @@ class NetB200:
 
 
 # ----------------------------------------------------------------------------------------------------
-# bench / smoke helpers (random-init weights come from the oracle's generator: test infrastructure)
+# bench / smoke helpers (random-init weights: modelgen.py; the oracle is imported by smoke() only, as the checker)
 # ----------------------------------------------------------------------------------------------------
 class _BenchNet:
     def __init__(self, net: NetB200, batch: int):
@@ -167,8 +167,8 @@ class _BenchNet:
 
 
 def bench_net(batch: int, h: int, w: int, device, model: str = "body_25", seed: int = 1234) -> _BenchNet:
-    from oracle import ref_net   # generator of the seeded random-init caffemodel (bench/smoke only)
-    proto, cm, _ = ref_net.build(model, seed)
+    from . import modelgen       # seeded random-init caffemodel (there is no network for the trained one)
+    proto, cm, _, _ = modelgen.build_files(model, seed)
     net = NetB200(proto, cm, gpuId=device.index or 0)
     net.initializationOnThread()
     return _BenchNet(net, batch)

@@ -29,52 +29,9 @@ import torch.nn.functional as F
 from . import caffe_io
 
 
-def random_init(netdef: caffe_io.NetDef, seed: int, out_rms: float = 0.15) -> Dict[str, List[np.ndarray]]:
-    """Seeded random-init weights that keep activations O(1) through the whole graph:
-    He-normal convs (gain for the activation that follows), small biases, PReLU slopes U(0.1, 0.3); convs
-    with no activation after them (the stage outputs) are scaled so their outputs have RMS ~ out_rms,
-    i.e. heat-map-like magnitudes (the 2e-2 max-abs tolerance of the north star is stated for such maps)."""
-    rng = np.random.default_rng(seed)
-    chan = {netdef.inputs[0]: netdef.input_dim[1] if len(netdef.input_dim) > 1 else 3}
-    follows: Dict[str, str] = {}
-    for L in netdef.layers:
-        if L.type in ("ReLU", "PReLU") and L.bottoms == L.tops:
-            follows.setdefault(L.bottoms[0] + "@" + str(id(L)), L.type)
-    blobs: Dict[str, List[np.ndarray]] = {}
-    layers = netdef.layers
-    for i, L in enumerate(layers):
-        if L.type == "Convolution":
-            cin, cout, k = chan[L.bottoms[0]], int(L.params["num_output"]), int(L.params["kernel_size"])
-            act = None
-            for A in layers[i + 1:]:
-                if A.bottoms == [L.tops[0]] and A.tops == [L.tops[0]] and A.type in ("ReLU", "PReLU"):
-                    act = A.type
-                    break
-                if L.tops[0] in A.bottoms:
-                    break
-            fan_in = cin * k * k
-            if act == "ReLU":
-                std = np.sqrt(2.0 / fan_in)
-            elif act == "PReLU":
-                std = np.sqrt(2.0 / (1.0 + 0.2 ** 2) / fan_in)
-            else:
-                std = out_rms * np.sqrt(1.0 / fan_in)
-            w = (rng.standard_normal((cout, cin, k, k)) * std).astype(np.float32)
-            b = rng.uniform(-0.05, 0.05, size=(cout,)).astype(np.float32) * (1.0 if act else out_rms)
-            blobs[L.name] = [w, b]
-            chan[L.tops[0]] = cout
-        elif L.type == "PReLU":
-            blobs[L.name] = [rng.uniform(0.1, 0.3, size=(chan[L.bottoms[0]],)).astype(np.float32)]
-        elif L.type == "Concat":
-            chan[L.tops[0]] = sum(chan[b] for b in L.bottoms)
-        else:
-            chan[L.tops[0]] = chan[L.bottoms[0]]
-    return blobs
-
-
-def save_caffemodel(path: str, netdef: caffe_io.NetDef, blobs: Dict[str, List[np.ndarray]]) -> None:
-    recs = [(L.name, L.type, blobs[L.name]) for L in netdef.layers if L.name in blobs]
-    caffe_io.write_caffemodel(path, netdef.name or "net", recs)
+# The seeded random-init generator and the caffemodel writer are host tooling shared with bench.py / smoke():
+# they live in openpose_b200/modelgen.py (the product never imports the oracle, the oracle may use the tooling).
+from openpose_b200.modelgen import random_init, save_caffemodel  # noqa: E402,F401
 
 
 class RefNet:
@@ -120,19 +77,8 @@ class RefNet:
 
 def build(model: str, seed: int = 1234, workdir: Optional[str] = None) -> Tuple[str, str, RefNet]:
     """Writes <workdir>/<model>.prototxt + .caffemodel (seeded random init) and returns (proto, model, RefNet)."""
-    from openpose_b200 import protogen
-    workdir = workdir or os.path.join(os.environ.get("TMPDIR", "/tmp"), "opb200_models")
-    os.makedirs(workdir, exist_ok=True)
-    text = protogen.generate(model)
-    proto = os.path.join(workdir, "%s_seed%d.prototxt" % (model, seed))
-    cm = os.path.join(workdir, "%s_seed%d.caffemodel" % (model, seed))
-    nd = caffe_io.load_netdef(text)
-    blobs = random_init(nd, seed)
-    if not (os.path.exists(proto) and os.path.exists(cm)):
-        with open(proto, "w") as f:
-            f.write(text)
-        save_caffemodel(cm + ".tmp", nd, blobs)
-        os.replace(cm + ".tmp", cm)
+    from openpose_b200 import modelgen
+    proto, cm, nd, blobs = modelgen.build_files(model, seed, workdir)
     return proto, cm, RefNet(nd, blobs)
 
 
