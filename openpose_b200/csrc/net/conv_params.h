@@ -26,7 +26,9 @@ namespace opb
         int tilesX, tilesY, numMTiles;        // numMTiles = N * tilesY * tilesX; a CTA works on PAIRS of M tiles
         int nTilesN;                          // Cout tiles of BN channels
         int cout;
-        int aTileBytes;                       // (16 + k - 1) * 1024
+        int kxSpan;                           // filter columns served by one activation box: k (halo box) or 1
+        int boxW;                             // box width in pixels = 8 + kxSpan - 1
+        int aTileBytes;                       // boxW * (16 + k - 1) * 128, rounded up to 1024
         int aStages, bStages;                 // pipeline depths (A stage = 2 tiles x aTileBytes, B stage = BN x 128 B)
         const float* bias;                    // [nTilesN * BN], zero padded
         const float* slope;                   // negative-side slope per channel: 0 = ReLU, a_c = PReLU, 1 = identity

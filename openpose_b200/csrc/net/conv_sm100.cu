@@ -86,6 +86,8 @@ namespace opb
         extern __shared__ uint8_t smemRaw[];
         uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smemRaw) + 1023) & ~uintptr_t(1023));
         const int aStageBytes = 2 * p.aTileBytes;
+        const uint32_t boxBytes = (uint32_t)p.boxW * (kConvTileH + p.k - 1) * 128u;   // what one TMA box delivers
+        const uint32_t groupPitch = (uint32_t)p.boxW * 128u;                         // bytes between pixel rows
         uint8_t* sA = smem;                                         // aStages x (tile0 | tile1)
         uint8_t* sB = sA + p.aStages * aStageBytes;                 // bStages x (BN x 128 B)
         uint8_t* sOut = sB + p.bStages * Cfg::kBBytes;              // staging for the TMA store
@@ -152,17 +154,21 @@ namespace opb
                         for (int c = 0; c < p.segChunks[s]; ++c, ++chunk)
                             for (int kx = 0; kx < p.k; ++kx)
                             {
-                                mbarWait(&aux->aEmpty[as], aPhase ^ 1);
-                                uint8_t* dst = sA + as * aStageBytes;
-                                mbarExpectTx(&aux->aFull[as], aStageBytes);
-                                tmaLoad4d(dst, &p.aMap[s], &aux->aFull[as], c * kConvBlockK, t0.x0 + kx - p.pad,
-                                          t0.y0 - p.pad, t0.n);
-                                tmaLoad4d(dst + p.aTileBytes, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
-                                          t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
-                                if (++as == p.aStages)
+                                if (kx % p.kxSpan == 0)
                                 {
-                                    as = 0;
-                                    aPhase ^= 1;
+                                    // one box serves kxSpan filter columns (and all k filter rows)
+                                    mbarWait(&aux->aEmpty[as], aPhase ^ 1);
+                                    uint8_t* dst = sA + as * aStageBytes;
+                                    mbarExpectTx(&aux->aFull[as], 2 * boxBytes);
+                                    tmaLoad4d(dst, &p.aMap[s], &aux->aFull[as], c * kConvBlockK, t0.x0 + kx - p.pad,
+                                              t0.y0 - p.pad, t0.n);
+                                    tmaLoad4d(dst + p.aTileBytes, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
+                                              t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
+                                    if (++as == p.aStages)
+                                    {
+                                        as = 0;
+                                        aPhase ^= 1;
+                                    }
                                 }
                                 const int kb0 = (chunk * p.k + kx) * p.k;
                                 for (int ky = 0; ky < p.k; ++ky)
@@ -189,7 +195,9 @@ namespace opb
                 constexpr uint32_t idesc = instrDescBf16(kConvBlockM, BN);
                 int as = 0, bs = 0, acc = 0;
                 uint32_t aPhase = 0, bPhase = 0, accPhase = 0;
-                const int numAx = p.chunksTotal * p.k;     // A stages consumed per work item
+                const int numAx = p.chunksTotal * (p.k / p.kxSpan);     // A stages consumed per work item
+                const uint64_t bBase = smemDescSw128(smemAddr(sB));
+                const uint64_t kyStep = (uint64_t)(p.boxW * 8);         // one box pixel row down, in 16-byte units
                 for (int work = blockIdx.x; work < numWork; work += gridDim.x)
                 {
                     mbarWait(&aux->tmemEmpty[acc], accPhase ^ 1);
@@ -199,27 +207,36 @@ namespace opb
                     for (int ax = 0; ax < numAx; ++ax)
                     {
                         mbarWait(&aux->aFull[as], aPhase);
-                        const uint32_t aAddr = smemAddr(sA + as * aStageBytes);
-                        for (int ky = 0; ky < p.k; ++ky)
+                        // tap (kxi, ky) = the 16 pixel rows starting at box pixel (kxi, ky): 8-pixel groups groupPitch
+                        // bytes apart, the first one (ky * boxW + kxi) * 128 bytes into the box. Descriptors are built
+                        // once per stage and advanced by adding 16-byte units to the start-address field.
+                        const uint64_t aBase0 = smemDescSw128(smemAddr(sA + as * aStageBytes), groupPitch);
+                        const uint64_t aBase1 = aBase0 + (uint64_t)(p.aTileBytes >> 4);
+                        uint32_t first = ax != 0;
+                        for (int kxi = 0; kxi < p.kxSpan; ++kxi)
                         {
-                            mbarWait(&aux->bFull[bs], bPhase);
-                            tcFenceAfter();
-                            // filter row ky = rows [8*ky, 8*ky + 128) of the halo box = +ky * 1024 bytes
-                            const uint64_t aDesc0 = smemDescSw128(aAddr + ky * 1024);
-                            const uint64_t aDesc1 = smemDescSw128(aAddr + p.aTileBytes + ky * 1024);
-                            const uint64_t bDesc = smemDescSw128(smemAddr(sB + bs * Cfg::kBBytes));
-                            const uint32_t first = (ax | ky) != 0;
+                            uint64_t aDesc0 = aBase0 + (uint64_t)(kxi * 8);
+                            uint64_t aDesc1 = aBase1 + (uint64_t)(kxi * 8);
+                            for (int ky = 0; ky < p.k; ++ky)
+                            {
+                                mbarWait(&aux->bFull[bs], bPhase);
+                                tcFenceAfter();
+                                const uint64_t bDesc = bBase + (uint64_t)(bs * (Cfg::kBBytes >> 4));
 #pragma unroll
-                            for (int kk = 0; kk < kConvBlockK / 16; ++kk)   // 16 bf16 = 32 bytes per MMA along K
-                            {
-                                mmaBf16(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
-                                mmaBf16(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
-                            }
-                            mmaCommit(&aux->bEmpty[bs]);          // weight slot free once these MMAs retire
-                            if (++bs == p.bStages)
-                            {
-                                bs = 0;
-                                bPhase ^= 1;
+                                for (int kk = 0; kk < kConvBlockK / 16; ++kk)   // 16 bf16 = 32 bytes per MMA along K
+                                {
+                                    mmaBf16(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                    mmaBf16(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                }
+                                first = 1;
+                                mmaCommit(&aux->bEmpty[bs]);      // weight slot free once these MMAs retire
+                                if (++bs == p.bStages)
+                                {
+                                    bs = 0;
+                                    bPhase ^= 1;
+                                }
+                                aDesc0 += kyStep;
+                                aDesc1 += kyStep;
                             }
                         }
                         mmaCommit(&aux->aEmpty[as]);              // activation slot free
@@ -359,12 +376,17 @@ namespace opb
     }
 
     // Pipeline depths for a given kernel size: 4 weight stages, as many activation stages as fit (2..4).
+    static int convTileBytes(int k, int kxSpan)
+    {
+        return ((kConvTileW + kxSpan - 1) * (kConvTileH + k - 1) * 128 + 1023) & ~1023;
+    }
+
     template <int BN>
-    static bool convSmemPlan(int k, int& aStages, int& bStages, int& smemBytes)
+    static bool convSmemPlan(int k, int kxSpan, int& aStages, int& bStages, int& smemBytes)
     {
         using Cfg = ConvCfg<BN>;
-        const int aStage = 2 * (kConvTileH + k - 1) * 1024;
-        bStages = BN <= 64 ? 6 : 4;
+        const int aStage = 2 * convTileBytes(k, kxSpan);
+        bStages = (BN <= 64 || kxSpan > 1) ? 6 : 4;
         const int fixed = Cfg::kStagingBytes + kAuxBytes + 1024 /*alignment slack*/ + bStages * Cfg::kBBytes;
         aStages = (kSmemLimit - fixed) / aStage;
         if (aStages > kMaxAStages)
@@ -377,9 +399,9 @@ namespace opb
     static opb200_status launchConvT(ConvParams& p, int gridCap, cudaStream_t st)
     {
         int smemBytes = 0;
-        if (!convSmemPlan<BN>(p.k, p.aStages, p.bStages, smemBytes))
+        if (!convSmemPlan<BN>(p.k, p.kxSpan, p.aStages, p.bStages, smemBytes))
             OPB_FAIL(OPB200_ERR_UNSUPPORTED, "conv: kernel size too large for the shared-memory pipeline");
-        p.aTileBytes = (kConvTileH + p.k - 1) * 1024;
+        p.aTileBytes = convTileBytes(p.k, p.kxSpan);
         static int configuredDev[64] = {0};   // attribute is per function per device; kSmemLimit covers every k
         int dev = 0;
         OPB_CUDA(cudaGetDevice(&dev));

@@ -732,6 +732,11 @@ namespace opb
             p.N = N;
             p.k = op.k;
             p.pad = op.pad;
+            // 3x3: one halo box per chunk serves all nine taps; larger kernels keep one box per filter column
+            // (a 7x7 halo box pair would not leave room for the weight pipeline)
+            static const bool haloBox = std::getenv("OPB200_CONV_NO_HALO") == nullptr;
+            p.kxSpan = (haloBox && op.k == 3) ? op.k : 1;
+            p.boxW = kConvTileW + p.kxSpan - 1;
             p.nSeg = (int)op.in.size();
             p.chunksTotal = op.chunksTotal;
             p.nTilesN = op.nTilesN;
@@ -746,7 +751,7 @@ namespace opb
             {
                 p.segChunks[s] = op.segChunks[s];
                 const opb200_status st = makeActivationMap(&p.aMap[s], viewPtr(op.in[s]), op.in[s].C, w, h, N,
-                                                           net.buffers[op.in[s].buf].C, kConvBlockK, kConvTileW,
+                                                           net.buffers[op.in[s].buf].C, kConvBlockK, p.boxW,
                                                            kConvTileH + op.k - 1, true);
                 if (st != OPB200_OK)
                     return st;

@@ -154,12 +154,12 @@ namespace sm100
 
     // UMMA shared-memory descriptor, K-major operand, 128-byte swizzle, rows of 64 bf16 (=128 B), 8-row
     // groups 1024 B apart (SBO). Field layout: cute/arch/mma_sm100_desc.hpp SmemDescriptor (version 1).
-    __device__ __forceinline__ uint64_t smemDescSw128(uint32_t saddr)
+    __device__ __forceinline__ uint64_t smemDescSw128(uint32_t saddr, uint32_t strideBytes = 1024)
     {
         uint64_t d = 0;
         d |= (uint64_t)((saddr & 0x3FFFF) >> 4);          // start address, bits [0,14)
         d |= (uint64_t)0 << 16;                           // leading byte offset: unused for swizzled K-major
-        d |= (uint64_t)(1024 >> 4) << 32;                 // stride byte offset, bits [32,46)
+        d |= (uint64_t)(strideBytes >> 4) << 32;          // stride byte offset (8-row group pitch), bits [32,46)
         d |= (uint64_t)1 << 46;                           // descriptor version (sm_100)
         d |= (uint64_t)2 << 61;                           // layout type SWIZZLE_128B
         return d;
