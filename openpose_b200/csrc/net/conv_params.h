@@ -30,10 +30,12 @@ namespace opb
         int boxW;                             // box width in pixels = 8 + kxSpan - 1
         int aTileBytes;                       // boxW * (16 + k - 1) * 128, rounded up to 1024
         int aStages, bStages;                 // pipeline depths (A stage = 2 tiles x aTileBytes, B stage = BN x 128 B)
+        int bResident;                        // 1: the whole weight tile fits in the B stages and is loaded once per CTA
         const float* bias;                    // [nTilesN * BN], zero padded
         const float* slope;                   // negative-side slope per channel: 0 = ReLU, a_c = PReLU, 1 = identity
         float* out32;                         // optional fp32 NCHW copy of the output (net_output members)
         int out32C, out32Off;                 // channels of that blob, channel offset of this layer in it
         int storeBf16;                        // 0: skip the bf16 NHWC store (nobody reads it)
+        int actMode;                          // 1: every slope is 0 (ReLU: add + max); 0: general per-channel slope
     };
 }

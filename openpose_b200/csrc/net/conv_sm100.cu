@@ -16,8 +16,9 @@
 //     (2 tiles x 4 k-steps), halving weight traffic per FLOP. 2 tiles x 2 accumulator stages x BN columns of TMEM.
 // The L2->SM operand stream, not the tensor pipe, bounds these layers (Cout <= 128): both measures cut bytes/FLOP.
 //
-// Roles (256 threads, persistent over work items): warp 0 = TMA producer, warp 1 = MMA issuer (one thread),
-// warp 2 = TMEM allocator, warps 4-7 = epilogue (thread t <-> TMEM lane t <-> pixel t of the tile).
+// Roles (384 threads, persistent over work items): warp 0 = TMA producer, warp 1 = MMA issuer (one thread),
+// warp 2 = TMEM allocator, warps 4-11 = epilogue (TMEM lane <-> pixel of the tile; two warps per lane quadrant split
+// the columns: short-K layers -- 1x1, Cin = 64 -- are paced by the epilogue, not by the tensor pipe).
 #include "../common.cuh"
 #include "conv_params.h"
 #include "sm100.cuh"
@@ -28,8 +29,8 @@ namespace opb
 {
     using namespace sm100;
 
-    constexpr int kConvThreads = 256;
-    constexpr int kMaxAStages = 4, kMaxBStages = 8;
+    constexpr int kConvThreads = 384;     // 4 role warps + 8 epilogue warps
+    constexpr int kMaxAStages = 4, kMaxBStages = 12;
     constexpr int kSmemLimit = 227 * 1024;
 
     template <int BN>
@@ -49,8 +50,7 @@ namespace opb
         uint64_t tmemFull[2], tmemEmpty[2];
         uint32_t tmemBase;
         uint32_t pad;
-        float bias[128];
-        float slope[128];
+        float2 biasSlope[128];                // (bias, negative-side slope) of the current Cout tile
     };
     constexpr int kAuxBytes = 2048;
     static_assert(sizeof(ConvAux) <= kAuxBytes, "aux block too large");
@@ -123,7 +123,7 @@ namespace opb
             for (int i = 0; i < 2; ++i)
             {
                 mbarInit(&aux->tmemFull[i], 1);
-                mbarInit(&aux->tmemEmpty[i], 128);
+                mbarInit(&aux->tmemEmpty[i], 256);
             }
             fenceBarrierInit();
         }
@@ -140,7 +140,8 @@ namespace opb
         if (warp == 0)
         {
             // ===================================== TMA producer ======================================
-            if (lane == 0)
+            // the whole (converged) warp runs the loop and waits; the elected lane issues
+            const bool leader = electOne();
             {
                 int as = 0, bs = 0;
                 uint32_t aPhase = 0, bPhase = 0;
@@ -159,11 +160,15 @@ namespace opb
                                     // one box serves kxSpan filter columns (and all k filter rows)
                                     mbarWait(&aux->aEmpty[as], aPhase ^ 1);
                                     uint8_t* dst = sA + as * aStageBytes;
-                                    mbarExpectTx(&aux->aFull[as], 2 * boxBytes);
-                                    tmaLoad4d(dst, &p.aMap[s], &aux->aFull[as], c * kConvBlockK, t0.x0 + kx - p.pad,
-                                              t0.y0 - p.pad, t0.n);
-                                    tmaLoad4d(dst + p.aTileBytes, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
-                                              t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
+                                    if (leader)
+                                    {
+                                        mbarExpectTx(&aux->aFull[as], 2 * boxBytes);
+                                        tmaLoad4d(dst, &p.aMap[s], &aux->aFull[as], c * kConvBlockK, t0.x0 + kx - p.pad,
+                                                  t0.y0 - p.pad, t0.n);
+                                        tmaLoad4d(dst + p.aTileBytes, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
+                                                  t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
+                                    }
+                                    __syncwarp();
                                     if (++as == p.aStages)
                                     {
                                         as = 0;
@@ -171,12 +176,18 @@ namespace opb
                                     }
                                 }
                                 const int kb0 = (chunk * p.k + kx) * p.k;
+                                if (p.bResident && work != (int)blockIdx.x)
+                                    continue;          // the whole weight tile already sits in shared memory
                                 for (int ky = 0; ky < p.k; ++ky)
                                 {
                                     mbarWait(&aux->bEmpty[bs], bPhase ^ 1);
-                                    mbarExpectTx(&aux->bFull[bs], Cfg::kBBytes);
-                                    tmaLoad2d(sB + bs * Cfg::kBBytes, &p.bMap, &aux->bFull[bs], (kb0 + ky) * kConvBlockK,
-                                              nt * BN);
+                                    if (leader)
+                                    {
+                                        mbarExpectTx(&aux->bFull[bs], Cfg::kBBytes);
+                                        tmaLoad2d(sB + bs * Cfg::kBBytes, &p.bMap, &aux->bFull[bs],
+                                                  (kb0 + ky) * kConvBlockK, nt * BN);
+                                    }
+                                    __syncwarp();
                                     if (++bs == p.bStages)
                                     {
                                         bs = 0;
@@ -190,7 +201,7 @@ namespace opb
         else if (warp == 1)
         {
             // ===================================== MMA issuer ========================================
-            if (lane == 0)
+            const bool leader = electOne();
             {
                 constexpr uint32_t idesc = instrDescBf16(kConvBlockM, BN);
                 int as = 0, bs = 0, acc = 0;
@@ -222,31 +233,41 @@ namespace opb
                                 mbarWait(&aux->bFull[bs], bPhase);
                                 tcFenceAfter();
                                 const uint64_t bDesc = bBase + (uint64_t)(bs * (Cfg::kBBytes >> 4));
-#pragma unroll
-                                for (int kk = 0; kk < kConvBlockK / 16; ++kk)   // 16 bf16 = 32 bytes per MMA along K
+                                if (leader)
                                 {
-                                    mmaBf16(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
-                                    mmaBf16(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+#pragma unroll
+                                    for (int kk = 0; kk < kConvBlockK / 16; ++kk)   // 16 bf16 = 32 bytes per MMA along K
+                                    {
+                                        mmaBf16(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                        mmaBf16(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                    }
+                                    if (!p.bResident)
+                                        mmaCommit(&aux->bEmpty[bs]);  // weight slot free once these MMAs retire
                                 }
+                                __syncwarp();
                                 first = 1;
-                                mmaCommit(&aux->bEmpty[bs]);      // weight slot free once these MMAs retire
+                                // resident weights: the slots are never recycled, their (only) phase stays complete
                                 if (++bs == p.bStages)
                                 {
                                     bs = 0;
-                                    bPhase ^= 1;
+                                    bPhase ^= p.bResident ? 0u : 1u;
                                 }
                                 aDesc0 += kyStep;
                                 aDesc1 += kyStep;
                             }
                         }
-                        mmaCommit(&aux->aEmpty[as]);              // activation slot free
+                        if (leader)
+                            mmaCommit(&aux->aEmpty[as]);          // activation slot free
+                        __syncwarp();
                         if (++as == p.aStages)
                         {
                             as = 0;
                             aPhase ^= 1;
                         }
                     }
-                    mmaCommit(&aux->tmemFull[acc]);               // both accumulators complete -> epilogue
+                    if (leader)
+                        mmaCommit(&aux->tmemFull[acc]);           // both accumulators complete -> epilogue
+                    __syncwarp();
                     if (++acc == 2)
                     {
                         acc = 0;
@@ -258,9 +279,17 @@ namespace opb
         else if (warp >= 4)
         {
             // ===================================== epilogue ==========================================
-            const int t = threadIdx.x - 128;          // 0..127 = TMEM lane = pixel of the tile
-            const int quad = warp & 3;                // warp (id % 4) may only touch lanes [32*quad, 32*quad+32)
+            // 8 warps: warp (id % 4) may only touch TMEM lanes [32*quad, 32*quad+32); the two warps of a quadrant
+            // split the 32-column pieces of the tile between them (half 0: even pieces, half 1: odd pieces), and
+            // each half stages and stores its own pieces (own named barrier, own bulk-store group).
+            const int quad = warp & 3;
+            const int half = (warp - 4) >> 2;
+            const int t = quad * 32 + lane;           // 0..127 = TMEM lane = pixel of the tile
+            const int et = threadIdx.x - 128;         // 0..255 over all epilogue threads
             const int tw = t % kConvTileW, th = t / kConvTileW;
+            const uint32_t halfBar = 2 + half;        // named barrier of this half (128 threads)
+            const bool issuer = (quad == 0 && lane == 0);
+            constexpr int kPieces = BN / 32;
             int acc = 0;
             uint32_t accPhase = 0;
             int lastNt = -1;
@@ -270,14 +299,11 @@ namespace opb
                 const int pair = work / p.nTilesN;
                 if (nt != lastNt)
                 {
-                    namedBarrier(1, 128);             // everybody is done with the previous table
-                    for (int i = t; i < BN; i += 128)
-                    {
-                        aux->bias[i] = __ldg(p.bias + nt * BN + i);
-                        aux->slope[i] = __ldg(p.slope + nt * BN + i);
-                    }
+                    namedBarrier(1, 256);             // everybody is done with the previous table
+                    for (int i = et; i < BN; i += 256)
+                        aux->biasSlope[i] = make_float2(__ldg(p.bias + nt * BN + i), __ldg(p.slope + nt * BN + i));
                     lastNt = nt;
-                    namedBarrier(1, 128);
+                    namedBarrier(1, 256);
                 }
                 mbarWait(&aux->tmemFull[acc], accPhase);
                 tcFenceAfter();
@@ -288,29 +314,39 @@ namespace opb
                     if (mt >= p.numMTiles)
                         break;                         // odd tile count: the last pair has no second tile
                     const TileCoord tc = tileCoord(p, mt);
-                    // the staging buffer is free once the previous tile's TMA store has read it
+                    // this half's staging pieces are free once its previous TMA stores have read them
                     if (p.storeBf16)
                     {
-                        if (t == 0)
+                        if (issuer)
                             tmaStoreWaitRead0();
-                        namedBarrier(1, 128);
+                        namedBarrier(halfBar, 128);
                     }
                     const uint32_t taddr =
                         tmemBase + (acc * 2 + j) * Cfg::kAccStride + ((uint32_t)(quad * 32) << 16);
                     const int x = tc.x0 + tw, y = tc.y0 + th;
                     const bool inImage = (x < p.W) && (y < p.H);
 #pragma unroll 1
-                    for (int q = 0; q < BN / 32; ++q)
+                    for (int q = half; q < kPieces; q += 2)
                     {
                         uint32_t v[32];
                         tmemLoad32(taddr + q * 32, v);
                         tmemLoadWait();
                         float f[32];
-#pragma unroll
-                        for (int i = 0; i < 32; ++i)
+                        if (p.actMode == 1)            // ReLU everywhere (the VGG trunk): add + max
                         {
-                            const float a = __uint_as_float(v[i]) + aux->bias[q * 32 + i];
-                            f[i] = a > 0.f ? a : a * aux->slope[q * 32 + i];
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                f[i] = fmaxf(__uint_as_float(v[i]) + aux->biasSlope[q * 32 + i].x, 0.f);
+                        }
+                        else
+                        {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                            {
+                                const float2 bs = aux->biasSlope[q * 32 + i];
+                                const float a = __uint_as_float(v[i]) + bs.x;
+                                f[i] = a > 0.f ? a : a * bs.y;
+                            }
                         }
                         if (p.out32 != nullptr && inImage)
                         {
@@ -346,10 +382,10 @@ namespace opb
                     if (p.storeBf16)
                     {
                         fenceProxyAsyncShared();
-                        namedBarrier(1, 128);
-                        if (t == 0)
+                        namedBarrier(halfBar, 128);
+                        if (issuer)
                         {
-                            for (int q = 0; q < BN / 32; ++q)
+                            for (int q = half; q < kPieces; q += 2)
                                 if (nt * BN + q * 32 < p.cout)
                                     tmaStore4d(&p.oMap, sOut + q * (kConvBlockM * 64), nt * BN + q * 32, tc.x0, tc.y0,
                                                tc.n);
@@ -366,7 +402,7 @@ namespace opb
                     accPhase ^= 1;
                 }
             }
-            if (t == 0)
+            if (issuer)
                 tmaStoreWaitAll();
         }
         tcFenceBefore();
@@ -381,12 +417,22 @@ namespace opb
         return ((kConvTileW + kxSpan - 1) * (kConvTileH + k - 1) * 128 + 1023) & ~1023;
     }
 
+    // bStagesAll = weight stages of one whole Cout tile (chunks * k * k); when there is a single Cout tile and they all
+    // fit next to two activation stages, the weights are loaded once per CTA and stay resident.
     template <int BN>
-    static bool convSmemPlan(int k, int kxSpan, int& aStages, int& bStages, int& smemBytes)
+    static bool convSmemPlan(int k, int kxSpan, int bStagesAll, bool singleNTile, int& aStages, int& bStages,
+                             int& resident, int& smemBytes)
     {
         using Cfg = ConvCfg<BN>;
         const int aStage = 2 * convTileBytes(k, kxSpan);
         bStages = (BN <= 64 || kxSpan > 1) ? 6 : 4;
+        resident = 0;
+        if (singleNTile && bStagesAll <= kMaxBStages &&
+            Cfg::kStagingBytes + kAuxBytes + 1024 + bStagesAll * Cfg::kBBytes + 2 * aStage <= kSmemLimit)
+        {
+            bStages = bStagesAll;
+            resident = 1;
+        }
         const int fixed = Cfg::kStagingBytes + kAuxBytes + 1024 /*alignment slack*/ + bStages * Cfg::kBBytes;
         aStages = (kSmemLimit - fixed) / aStage;
         if (aStages > kMaxAStages)
@@ -399,7 +445,8 @@ namespace opb
     static opb200_status launchConvT(ConvParams& p, int gridCap, cudaStream_t st)
     {
         int smemBytes = 0;
-        if (!convSmemPlan<BN>(p.k, p.kxSpan, p.aStages, p.bStages, smemBytes))
+        if (!convSmemPlan<BN>(p.k, p.kxSpan, p.chunksTotal * p.k * p.k, p.nTilesN == 1, p.aStages, p.bStages, p.bResident,
+                              smemBytes))
             OPB_FAIL(OPB200_ERR_UNSUPPORTED, "conv: kernel size too large for the shared-memory pipeline");
         p.aTileBytes = convTileBytes(p.k, p.kxSpan);
         static int configuredDev[64] = {0};   // attribute is per function per device; kSmemLimit covers every k

@@ -744,6 +744,10 @@ namespace opb
             p.bias = op.dBias;
             p.slope = op.dSlope;
             p.storeBf16 = op.storeBf16 ? 1 : 0;
+            p.actMode = 1;
+            for (int co = 0; co < op.cout; ++co)
+                if (op.hostSlope[co] != 0.f)
+                    p.actMode = 0;
             p.out32 = op.out32Off >= 0 ? net.dOut32 : nullptr;
             p.out32C = net.outC;
             p.out32Off = op.out32Off >= 0 ? op.out32Off : 0;
