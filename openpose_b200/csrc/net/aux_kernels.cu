@@ -5,6 +5,7 @@
 //                      (reference: 3rdparty/caffe/src/caffe/layers/pooling_layer.cpp:91-97,141-175)
 //   nhwcToNchwKernel : bf16 NHWC view -> fp32 NCHW (only for output blobs that no conv epilogue wrote directly)
 #include "../common.cuh"
+#include <climits>
 #include "net_kernels.h"
 #include <cuda_bf16.h>
 
@@ -188,7 +189,7 @@ namespace opb
                 wb[nt][s][1] = v.y;
             }
         // the 8 patch elements this thread gathers per pixel: j = 16*s + 2*q + {0,1,8,9}
-        int jOff[8], jDy[8], jDx[8];
+        int jOff[8], jDy[8], jDx[8];   // offset of tap j relative to the pixel (or -1), and its (dy, dx)
 #pragma unroll
         for (int e = 0; e < 8; ++e)
         {
@@ -196,42 +197,53 @@ namespace opb
             if (j < K)
             {
                 const int c = j / kk, r = j - c * kk;
-                jOff[e] = c * H * W;
                 jDy[e] = r / k - pad;
                 jDx[e] = r % k - pad;
+                jOff[e] = c * H * W + jDy[e] * W + jDx[e];
             }
             else
             {
-                jOff[e] = -1;
+                jOff[e] = INT_MIN;           // K padding: contributes zero
                 jDy[e] = jDx[e] = 0;
             }
         }
-        const long long total = (long long)N * H * W;
-        const long long step = (long long)gridDim.x * kFirstWarps * 32;
-        for (long long p0 = ((long long)blockIdx.x * kFirstWarps + warp) * 32; p0 < total; p0 += step)
+        bool relu = true;                    // every slope zero: add + max
+        for (int i = 0; i < cout; ++i)
+            relu = relu && (__ldg(slope + i) == 0.f);
+        // work unit = 32 consecutive pixels of one image row: no per-pixel division, and a unit away from the image
+        // border gathers its patches without any bounds test
+        const int xBlocks = (W + 31) >> 5;
+        const int units = N * H * xBlocks;
+        for (int u = blockIdx.x * kFirstWarps + warp; u < units; u += gridDim.x * kFirstWarps)
         {
+            const int row = u / xBlocks, xb = u - row * xBlocks;
+            const int n = row / H, y = row - n * H;
+            const int x0 = xb << 5;
+            const float* base = src + (size_t)n * C * H * W + (size_t)y * W;
+            const bool interior = (y >= pad) && (y < H - pad) && (x0 >= pad) && (x0 + 31 + pad < W);
+            const long long p0 = (long long)row * W + x0;     // first pixel of the unit in (n, y, x) raster order
             uint32_t a[2][2][4];   // [m tile][k step][fragment register]
 #pragma unroll
             for (int t = 0; t < 2; ++t)
 #pragma unroll
                 for (int hrow = 0; hrow < 2; ++hrow)
                 {
-                    const long long p = p0 + t * 16 + hrow * 8 + g;
+                    const int x = x0 + t * 16 + hrow * 8 + g;
                     float v[8];
-#pragma unroll
-                    for (int e = 0; e < 8; ++e)
-                        v[e] = 0.f;
-                    if (p < total)
+                    if (interior)
                     {
-                        const int x = (int)(p % W);
-                        const int y = (int)((p / W) % H);
-                        const long long base = (p / ((long long)W * H)) * (long long)C * H * W;
+#pragma unroll
+                        for (int e = 0; e < 8; ++e)
+                            v[e] = jOff[e] != INT_MIN ? __ldg(base + x + jOff[e]) : 0.f;
+                    }
+                    else
+                    {
 #pragma unroll
                         for (int e = 0; e < 8; ++e)
                         {
                             const int yy = y + jDy[e], xx = x + jDx[e];
-                            if (jOff[e] >= 0 && yy >= 0 && yy < H && xx >= 0 && xx < W)
-                                v[e] = __ldg(src + base + jOff[e] + (long long)yy * W + xx);
+                            v[e] = (jOff[e] != INT_MIN && x < W && yy >= 0 && yy < H && xx >= 0 && xx < W)
+                                       ? __ldg(base + x + jOff[e]) : 0.f;
                         }
                     }
                     // e = 4*s + 2*hi8 + lo : registers a0 (row g, k lo), a1 (row g+8), a2 (row g, k+8), a3 (row g+8, k+8)
@@ -261,10 +273,20 @@ namespace opb
                     o[1] = c[1] + b2.y;
                     o[2] = c[2] + b2.x;
                     o[3] = c[3] + b2.y;
-                    o[0] = o[0] > 0.f ? o[0] : o[0] * s2.x;
-                    o[1] = o[1] > 0.f ? o[1] : o[1] * s2.y;
-                    o[2] = o[2] > 0.f ? o[2] : o[2] * s2.x;
-                    o[3] = o[3] > 0.f ? o[3] : o[3] * s2.y;
+                    if (relu)
+                    {
+                        o[0] = fmaxf(o[0], 0.f);
+                        o[1] = fmaxf(o[1], 0.f);
+                        o[2] = fmaxf(o[2], 0.f);
+                        o[3] = fmaxf(o[3], 0.f);
+                    }
+                    else
+                    {
+                        o[0] = o[0] > 0.f ? o[0] : o[0] * s2.x;
+                        o[1] = o[1] > 0.f ? o[1] : o[1] * s2.y;
+                        o[2] = o[2] > 0.f ? o[2] : o[2] * s2.x;
+                        o[3] = o[3] > 0.f ? o[3] : o[3] * s2.y;
+                    }
                     *reinterpret_cast<uint32_t*>(st + (t * 16 + g) * kFirstPitch + nt * 16 + q * 4) = packBf16(o[0], o[1]);
                     *reinterpret_cast<uint32_t*>(st + (t * 16 + g + 8) * kFirstPitch + nt * 16 + q * 4) = packBf16(o[2], o[3]);
                 }
@@ -275,7 +297,7 @@ namespace opb
             for (int i = lane; i < chunks; i += 32)
             {
                 const int px = i / nTiles, ch = i - px * nTiles;
-                if (p0 + px < total)
+                if (x0 + px < W)
                     *reinterpret_cast<uint4*>(dst + (p0 + px) * dstStride + ch * 8) =
                         *reinterpret_cast<const uint4*>(st + px * kFirstPitch + ch * 16);
             }
@@ -289,8 +311,9 @@ namespace opb
     {
         OPB_REQUIRE(C * k * k <= 32 && cout % 8 == 0 && cout <= 64 && dstStride % 8 == 0,
                     "first conv: needs Cin*k*k <= 32 and Cout a multiple of 8, at most 64");
-        const long long total = (long long)N * H * W;
-        const long long want = (total + kFirstWarps * 32 - 1) / (kFirstWarps * 32);
+        const long long units = (long long)N * H * ((W + 31) / 32);
+        OPB_REQUIRE(units < (1ll << 31), "first conv: input too large");
+        const long long want = (units + kFirstWarps - 1) / kFirstWarps;
         const int blocks = (int)(want < 148 * 8 ? want : 148 * 8);
         firstConvKernel<<<blocks > 0 ? blocks : 1, kFirstWarps * 32, 0, st>>>(
             static_cast<__nv_bfloat16*>(dst), src, wfrag, bias, slope, N, C, H, W, k, pad, cout, dstStride);
