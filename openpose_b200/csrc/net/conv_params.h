@@ -36,6 +36,7 @@ namespace opb
         float* out32;                         // optional fp32 NCHW copy of the output (net_output members)
         int out32C, out32Off;                 // channels of that blob, channel offset of this layer in it
         int storeBf16;                        // 0: skip the bf16 NHWC store (nobody reads it)
+        int poolFused;                        // 1: 2x2/2 MAX pooling in the epilogue; oMap is the pooled blob, box (32, 4, 8, 1)
         int actMode;                          // 1: every slope is 0 (ReLU: add + max); 0: general per-channel slope
     };
 }

@@ -315,7 +315,7 @@ namespace opb
                         break;                         // odd tile count: the last pair has no second tile
                     const TileCoord tc = tileCoord(p, mt);
                     // this half's staging pieces are free once its previous TMA stores have read them
-                    if (p.storeBf16)
+                    if (p.storeBf16 | p.poolFused)
                     {
                         if (issuer)
                             tmaStoreWaitRead0();
@@ -358,11 +358,32 @@ namespace opb
                                 if (cBase + i < p.cout)
                                     o[i * plane] = f[i];
                         }
-                        if (p.storeBf16)
+                        if (p.poolFused)
                         {
-                            // row t of a 128 x 64-byte piece; 16-byte chunk c lands at c ^ ((t >> 1) & 3) (SWIZZLE_64B)
-                            uint8_t* row = sOut + q * (kConvBlockM * 64) + t * 64;
-                            const int sw = (t >> 1) & 3;
+                            // fused 2x2 / stride 2 MAX pooling (Caffe ceil mode: windows are clipped at the image edge):
+                            // the tile origin is even, so a window never straddles tiles, and its four pixels are
+                            // lanes l, l^1 (x) and l^8 (y) of this warp. Pixels outside the image do not take part.
+                            if (!inImage)
+                            {
+#pragma unroll
+                                for (int i = 0; i < 32; ++i)
+                                    f[i] = __int_as_float(0xff800000);
+                            }
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                            {
+                                float m = fmaxf(f[i], __shfl_xor_sync(0xffffffffu, f[i], 1));
+                                f[i] = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
+                            }
+                        }
+                        if (p.storeBf16 | p.poolFused)
+                        {
+                            // row t of a 128 x 64-byte piece; 16-byte chunk c lands at c ^ ((t >> 1) & 3) (SWIZZLE_64B).
+                            // Pooled: the window anchors (even x, even y) write row (y/2)*4 + x/2 of a 32-row piece.
+                            const int r = p.poolFused ? ((th >> 1) * (kConvTileW / 2) + (tw >> 1)) : t;
+                            uint8_t* row = sOut + q * (kConvBlockM * 64) + r * 64;
+                            const int sw = (r >> 1) & 3;
+                            if (!p.poolFused || ((tw | th) & 1) == 0)
 #pragma unroll
                             for (int c = 0; c < 4; ++c)
                             {
@@ -379,16 +400,17 @@ namespace opb
                             }
                         }
                     }
-                    if (p.storeBf16)
+                    if (p.storeBf16 | p.poolFused)
                     {
                         fenceProxyAsyncShared();
                         namedBarrier(halfBar, 128);
                         if (issuer)
                         {
+                            // pooled: oMap describes the pooled blob with a (32 ch, 4, 8) box
+                            const int sx = p.poolFused ? tc.x0 >> 1 : tc.x0, sy = p.poolFused ? tc.y0 >> 1 : tc.y0;
                             for (int q = half; q < kPieces; q += 2)
                                 if (nt * BN + q * 32 < p.cout)
-                                    tmaStore4d(&p.oMap, sOut + q * (kConvBlockM * 64), nt * BN + q * 32, tc.x0, tc.y0,
-                                               tc.n);
+                                    tmaStore4d(&p.oMap, sOut + q * (kConvBlockM * 64), nt * BN + q * 32, sx, sy, tc.n);
                             tmaStoreCommit();
                         }
                     }

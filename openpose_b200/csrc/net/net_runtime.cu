@@ -128,6 +128,9 @@ namespace opb
         float *dBias = nullptr, *dSlope = nullptr;
         int out32Off = -1;
         bool storeBf16 = true;
+        bool poolFused = false;     // a 2x2/2 MAX pooling that only this conv feeds runs in its epilogue
+        View poolOut;               //   ... writing this view at level poolLevel
+        int poolLevel = 0;
         double flopsPerPixel = 0;   // algorithmic: 2 * cout * cin * k * k
         // pool
         int stride = 1;
@@ -630,6 +633,35 @@ namespace opb
                     read = read || overlaps(v, op.out);
             op.storeBf16 = read || op.out32Off < 0;
         }
+        // ---- fold 2x2 / stride 2 poolings into the epilogue of the conv that feeds them ----------------------
+        // (conv -> in-place ReLU -> pool with no other reader of the conv output: the full-resolution blob is
+        // then never written or read back; kernel: conv_sm100.cu, poolFused)
+        static const bool fusePools = std::getenv("OPB200_NO_POOL_FUSION") == nullptr;
+        for (size_t pi = 0; fusePools && pi < net.ops.size(); ++pi)
+        {
+            const Op& pool = net.ops[pi];
+            if (pool.kind != OP_POOL || pool.k != 2 || pool.stride != 2 || pool.in.size() != 1)
+                continue;
+            int producer = -1, readers = 0;
+            for (size_t ci = 0; ci < net.ops.size(); ++ci)
+            {
+                const Op& c = net.ops[ci];
+                if (c.kind == OP_CONV && c.out.buf == pool.in[0].buf && c.out.cOff == pool.in[0].cOff &&
+                    c.out.C == pool.in[0].C && c.out32Off < 0)
+                    producer = (int)ci;
+                for (const View& v : c.in)
+                    readers += overlaps(v, pool.in[0]) ? 1 : 0;
+            }
+            if (producer < 0 || readers != 1 || (size_t)producer > pi)
+                continue;
+            Op& conv = net.ops[producer];
+            conv.poolFused = true;
+            conv.poolOut = pool.out;
+            conv.poolLevel = pool.outLevel;
+            conv.storeBf16 = false;
+            net.ops.erase(net.ops.begin() + pi);
+            --pi;
+        }
         return OPB200_OK;
     }
 
@@ -763,8 +795,14 @@ namespace opb
             opb200_status st = makeWeightMap(&p.bMap, op.dW, op.kTotal, op.nTilesN * op.bn, op.bn);
             if (st != OPB200_OK)
                 return st;
-            st = makeActivationMap(&p.oMap, viewPtr(op.out), op.out.C, w, h, N, net.buffers[op.out.buf].C, 32,
-                                   kConvTileW, kConvTileH, false);
+            p.poolFused = op.poolFused ? 1 : 0;
+            if (op.poolFused)   // the pooled blob, one (32 ch, 4, 8) box per tile
+                st = makeActivationMap(&p.oMap, viewPtr(op.poolOut), op.poolOut.C, net.lvW[op.poolLevel],
+                                       net.lvH[op.poolLevel], N, net.buffers[op.poolOut.buf].C, 32, kConvTileW / 2,
+                                       kConvTileH / 2, false);
+            else
+                st = makeActivationMap(&p.oMap, viewPtr(op.out), op.out.C, w, h, N, net.buffers[op.out.buf].C, 32,
+                                       kConvTileW, kConvTileH, false);
             if (st != OPB200_OK)
                 return st;
             net.flopsPerForward += op.flopsPerPixel * (double)N * h * w;
@@ -1090,9 +1128,10 @@ extern "C" opb200_status opb200_net_describe(const char* prototxt, const char* c
             std::snprintf(line, sizeof(line), "%s%d:%d:%d", segs.empty() ? "" : ",", v.buf, v.cOff, v.C);
             segs += line;
         }
-        std::snprintf(line, sizeof(line), "%s %s cin=%d cout=%d k=%d bn=%d tilesN=%d segs=[%s] out=%d:%d:%d out32=%d bf16=%d\n",
+        const View& ov = op.poolFused ? op.poolOut : op.out;
+        std::snprintf(line, sizeof(line), "%s %s cin=%d cout=%d k=%d bn=%d tilesN=%d segs=[%s] out=%d:%d:%d out32=%d bf16=%d pool=%d\n",
                       kinds[op.kind], op.name.c_str(), op.cin, op.cout, op.k, op.bn, op.nTilesN, segs.c_str(),
-                      op.out.buf, op.out.cOff, op.out.C, op.out32Off, op.storeBf16 ? 1 : 0);
+                      ov.buf, ov.cOff, ov.C, op.out32Off, op.storeBf16 ? 1 : 0, op.poolFused ? 1 : 0);
         out += line;
     }
     std::snprintf(line, sizeof(line), "output %s C=%d buffers=%d levels=%d\n", net.lastBlobName.c_str(), net.outC,

@@ -28,7 +28,9 @@ def main():
         else:
             cin, cout, k = int(kv["cin"]), int(kv["cout"]), int(kv["k"])
             flops = 2.0 * batch * h * w * cin * cout * k * k
-            desc = "%s %d->%d k%d @%dx%d" % (op[1], cin, cout, k, h, w)
+            desc = "%s %d->%d k%d @%dx%d%s" % (op[1], cin, cout, k, h, w, "+pool" if kv.get("pool") == "1" else "")
+            if kv.get("pool") == "1":
+                h, w = (h + 1) // 2, (w + 1) // 2
         assert ("Pool" in r["Kernel Name"]) == (kind == "pool"), (op, r["Kernel Name"])
         table.append((ns, flops, desc, r["Kernel Name"][:28]))
         total += ns
