@@ -11,6 +11,7 @@ namespace opb
     constexpr int kConvBlockM = kConvTileW * kConvTileH;
     constexpr int kConvBlockK = 64;       // channels per k-block = one 128-byte swizzled smem row
     constexpr int kConvMaxKernel = 7;
+    constexpr int kConvMaxChunks = 32;    // 64-channel chunks of one conv input (Cin <= 2048)
 
     struct ConvParams
     {
@@ -19,6 +20,7 @@ namespace opb
         CUtensorMap bMap;                     // weights: dims (Ktotal, CoutPad) bf16, box (64, BN), SWIZZLE_128B
         CUtensorMap oMap;                     // output view: dims (Cout, W, H, N) bf16, box (32, 8, 16, 1), SWIZZLE_64B
         int segChunks[kConvMaxSegments];      // 64-channel chunks per segment (last chunk zero-filled by TMA)
+        uint8_t chunkSteps[kConvMaxChunks];               // per chunk (all segments in order): 16-channel k-steps with real channels, 1..4
         int nSeg;
         int chunksTotal;
         int k, pad;                           // square odd kernel, "same" padding

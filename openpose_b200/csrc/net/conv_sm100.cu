@@ -206,7 +206,8 @@ namespace opb
                 constexpr uint32_t idesc = instrDescBf16(kConvBlockM, BN);
                 int as = 0, bs = 0, acc = 0;
                 uint32_t aPhase = 0, bPhase = 0, accPhase = 0;
-                const int numAx = p.chunksTotal * (p.k / p.kxSpan);     // A stages consumed per work item
+                const int axPerChunk = p.k / p.kxSpan;
+                const int numAx = p.chunksTotal * axPerChunk;           // A stages consumed per work item
                 const uint64_t bBase = smemDescSw128(smemAddr(sB));
                 const uint64_t kyStep = (uint64_t)(p.boxW * 8);         // one box pixel row down, in 16-byte units
                 for (int work = blockIdx.x; work < numWork; work += gridDim.x)
@@ -215,8 +216,16 @@ namespace opb
                     tcFenceAfter();
                     const uint32_t tmemD0 = tmemBase + (acc * 2) * Cfg::kAccStride;
                     const uint32_t tmemD1 = tmemD0 + Cfg::kAccStride;
+                    int chunk = 0, axInChunk = 0;
                     for (int ax = 0; ax < numAx; ++ax)
                     {
+                        // 16-channel k-steps that hold real channels in this chunk (the rest is TMA zero fill)
+                        const int steps = p.chunkSteps[chunk];
+                        if (++axInChunk == axPerChunk)
+                        {
+                            axInChunk = 0;
+                            ++chunk;
+                        }
                         mbarWait(&aux->aFull[as], aPhase);
                         // tap (kxi, ky) = the 16 pixel rows starting at box pixel (kxi, ky): 8-pixel groups groupPitch
                         // bytes apart, the first one (ky * boxW + kxi) * 128 bytes into the box. Descriptors are built
@@ -237,10 +246,11 @@ namespace opb
                                 {
 #pragma unroll
                                     for (int kk = 0; kk < kConvBlockK / 16; ++kk)   // 16 bf16 = 32 bytes per MMA along K
-                                    {
-                                        mmaBf16(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
-                                        mmaBf16(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
-                                    }
+                                        if (kk < steps)
+                                        {
+                                            mmaBf16(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                            mmaBf16(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                        }
                                     if (!p.bResident)
                                         mmaCommit(&aux->bEmpty[bs]);  // weight slot free once these MMAs retire
                                 }

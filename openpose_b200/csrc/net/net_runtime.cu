@@ -783,9 +783,16 @@ namespace opb
             p.out32 = op.out32Off >= 0 ? net.dOut32 : nullptr;
             p.out32C = net.outC;
             p.out32Off = op.out32Off >= 0 ? op.out32Off : 0;
-            for (int s = 0; s < p.nSeg; ++s)
+            if (op.chunksTotal > kConvMaxChunks)
+                OPB_FAIL(OPB200_ERR_UNSUPPORTED, "conv: more than 2048 input channels");
+            for (int s = 0, chunk = 0; s < p.nSeg; ++s)
             {
                 p.segChunks[s] = op.segChunks[s];
+                for (int c = 0; c < op.segChunks[s]; ++c, ++chunk)
+                {
+                    const int valid = std::min(kConvBlockK, op.in[s].C - c * kConvBlockK);
+                    p.chunkSteps[chunk] = (uint8_t)((valid + 15) / 16);
+                }
                 const opb200_status st = makeActivationMap(&p.aMap[s], viewPtr(op.in[s]), op.in[s].C, w, h, N,
                                                            net.buffers[op.in[s].buf].C, kConvBlockK, p.boxW,
                                                            kConvTileH + op.k - 1, true);
