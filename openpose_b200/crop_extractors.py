@@ -1,0 +1,253 @@
+"""Host-side mirror of the reference's hand / face keypoint extractors for the hot path:
+crop -> net -> resizeAndMerge x8 -> maximum -> affine back-projection.
+
+Mirrors (reference files relative to zengjianping/openpose, same argument meaning / error text):
+  HandExtractorB200.forwardPass <- HandExtractorCaffe::forwardPass  src/openpose/hand/handExtractorCaffe.cpp:305-464
+      crop_frame                <- cropFrame                        handExtractorCaffe.cpp:44-76
+      connect_keypoints         <- connectKeypoints                 handExtractorCaffe.cpp:78-102
+  FaceExtractorB200.forwardPass <- FaceExtractorCaffe::forwardPass  src/openpose/face/faceExtractorCaffe.cpp:175-300
+  get_average_score             <- getAverageScore                  src/openpose/utilities/keypoint.cpp:352-373
+  u_char_to_float               <- uCharCvMatToFloatPtr(normalize=1) src/openpose/utilities/openCv.cpp:57-130
+
+B200-first difference (results per crop are the reference's): the reference runs its net once per crop, batch 1,
+one after the other; here every valid crop of the frame (both hands of every person, every scale) goes through
+ONE batched net forward, one resize launch and one maximum launch -- the unit SURVEY 8(e) shards across GPUs.
+The crop itself (cv::warpAffine, INTER_LINEAR | WARP_INVERSE_MAP) stays on the host as in the reference
+(SURVEY 8(f) rank 1 moves it to the device).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import net as netmod
+from . import post
+from ._lib import Opb200Error
+from .pose_extractor import HeatMapType, ScaleMode, maximum_top_shape, positive_int_round, remap_heat_maps, \
+    resize_and_merge_top_shape
+
+HAND_NUMBER_PARTS = 21           # include/openpose/hand/handParameters.hpp:11
+HAND_CCN_DECREASE_FACTOR = 8.0   # handParameters.hpp:43
+FACE_NUMBER_PARTS = 70           # include/openpose/face/faceParameters.hpp:11
+FACE_CCN_DECREASE_FACTOR = 8.0   # faceParameters.hpp:24
+
+Rect = Tuple[float, float, float, float]   # x, y, width, height (op::Rectangle<float>)
+
+
+def u_char_to_float(image_hwc: np.ndarray) -> np.ndarray:
+    """uint8 H x W x C -> float32 C x H x W, x/256 - 0.5 (exact in float: the AVX fmadd and the scalar path agree)."""
+    return (image_hwc.transpose(2, 0, 1).astype(np.float32) * np.float32(1.0 / 256.0)) - np.float32(0.5)
+
+
+def crop_frame(cv_input: np.ndarray, rect: Rect, net_input_side: int, net_output_size: Tuple[int, int],
+               mirror: bool) -> Tuple[np.ndarray, np.ndarray]:
+    """-> (crop (3,H,W) float32, affine 2x3 float64): crop pixel (u,v) <- image (a00*u + a02, a11*v + a12)."""
+    import cv2
+    scale = np.float32(rect[2]) / np.float32(net_input_side)
+    m = np.eye(2, 3, dtype=np.float64)
+    m[0, 0] = -float(scale) if mirror else float(scale)
+    m[1, 1] = float(scale)
+    m[0, 2] = float(np.float32(rect[0]) + np.float32(rect[2])) if mirror else float(np.float32(rect[0]))
+    m[1, 2] = float(np.float32(rect[1]))
+    img = cv2.warpAffine(cv_input, m, (int(net_output_size[0]), int(net_output_size[1])),
+                         flags=cv2.INTER_LINEAR | cv2.WARP_INVERSE_MAP, borderMode=cv2.BORDER_CONSTANT,
+                         borderValue=(0, 0, 0))
+    return u_char_to_float(img), m
+
+
+def connect_keypoints(peaks: np.ndarray, affine: np.ndarray) -> np.ndarray:
+    """peaks (parts, 3) in crop pixels -> (parts, 3) in image pixels, double-precision affine then float."""
+    x, y = peaks[:, 0].astype(np.float64), peaks[:, 1].astype(np.float64)
+    out = np.empty_like(peaks, dtype=np.float32)
+    out[:, 0] = (affine[0, 0] * x + affine[0, 1] * y + affine[0, 2]).astype(np.float32)
+    out[:, 1] = (affine[1, 0] * x + affine[1, 1] * y + affine[1, 2]).astype(np.float32)
+    out[:, 2] = peaks[:, 2]
+    return out
+
+
+def get_average_score(keypoints: np.ndarray) -> np.float32:
+    """float accumulation in part order, then / numberKeypoints."""
+    s = np.float32(0)
+    for v in keypoints[:, 2]:
+        s = np.float32(s + np.float32(v))
+    return np.float32(s / np.float32(keypoints.shape[0]))
+
+
+def recenter(rect: Rect, new_w: float, new_h: float) -> Rect:
+    f = np.float32
+    cx = f(f(rect[0]) + f(rect[2]) / f(2))
+    cy = f(f(rect[1]) + f(rect[3]) / f(2))
+    return (float(cx - f(f(new_w) / f(2.0))), float(cy - f(f(new_h) / f(2.0))), float(new_w), float(new_h))
+
+
+class _CropNet:
+    """Net + resize + maximum on a batch of crops (what detectHandKeypoints does per crop)."""
+
+    def __init__(self, proto: str, model: str, gpu: int, decrease_factor: float):
+        self.net = netmod.NetB200(proto, model, gpuId=gpu)
+        self.gpu, self.factor = gpu, decrease_factor
+        self.heat: Optional[torch.Tensor] = None
+        self.peaks: Optional[torch.Tensor] = None
+
+    def init(self) -> None:
+        self.net.initializationOnThread()
+
+    def run(self, crops: np.ndarray) -> np.ndarray:
+        """crops (N,3,H,W) float32 -> peaks (N, parts, 3) in crop pixels (host)."""
+        self.net.forwardPass(np.ascontiguousarray(crops, np.float32))
+        out = self.net.getOutputBlobArray()
+        top = resize_and_merge_top_shape(list(out.shape), self.factor, 1.0, False)
+        if self.heat is None or list(self.heat.shape) != top:
+            dev = torch.device("cuda", self.gpu)
+            self.heat = torch.empty(top, dtype=torch.float32, device=dev)
+            self.peaks = torch.empty(maximum_top_shape(top), dtype=torch.float32, device=dev)
+        post.resize_and_merge_gpu(self.heat, [out])
+        post.maximum_gpu(self.peaks, self.heat)
+        return self.peaks[:, 0].cpu().numpy()
+
+
+def _heat_maps_for_person(heat_crop: torch.Tensor, parts: int, mode: ScaleMode) -> np.ndarray:
+    """updateHandHeatMapsForPerson / updateFaceHeatMapsForPerson: the part channels, body-part remap rules."""
+    return remap_heat_maps(heat_crop[:parts], None, None, mode)[0].cpu().numpy()
+
+
+class HandExtractorB200:
+    def __init__(self, netInputSize: Tuple[int, int], netOutputSize: Tuple[int, int], caffeProto: str,
+                 caffeTrainedModel: str, gpuId: int = 0, numberScales: int = 1, rangeScales: float = 0.4,
+                 heatMapTypes: Sequence[HeatMapType] = (), heatMapScaleMode: ScaleMode = ScaleMode.ZeroToOneFixedAspect):
+        if tuple(netInputSize) != tuple(netOutputSize):      # handExtractorNet.cpp ctor check
+            raise Opb200Error("Net input and output size must be equal.")
+        self.mNetOutputSize = (int(netOutputSize[0]), int(netOutputSize[1]))
+        self.mMultiScaleNumberAndRange = (int(numberScales), float(rangeScales))
+        self.mHeatMapTypes, self.mHeatMapScaleMode = list(heatMapTypes), ScaleMode(heatMapScaleMode)
+        self._net = _CropNet(caffeProto, caffeTrainedModel, gpuId, HAND_CCN_DECREASE_FACTOR)
+        self.mHandKeypoints = [np.zeros((0, HAND_NUMBER_PARTS, 3), np.float32) for _ in range(2)]
+        self.mHeatMaps: List[Optional[np.ndarray]] = [None, None]
+        self.mEnabled = True
+
+    def initializationOnThread(self) -> None:
+        self._net.init()
+
+    def getHandKeypoints(self) -> List[np.ndarray]:
+        return self.mHandKeypoints
+
+    def getHeatMaps(self) -> List[Optional[np.ndarray]]:
+        return self.mHeatMaps
+
+    def forwardPass(self, handRectangles: Sequence[Sequence[Rect]], cvInputData: np.ndarray) -> None:
+        """handRectangles[person] = (left, right) rectangles; cvInputData: H x W x 3 uint8 BGR frame."""
+        if not self.mEnabled or len(handRectangles) == 0:
+            self.mHandKeypoints = [np.zeros((0, HAND_NUMBER_PARTS, 3), np.float32) for _ in range(2)]
+            return
+        if cvInputData is None or cvInputData.size == 0:
+            raise Opb200Error("Empty cvInputData.")
+        side = min(self.mNetOutputSize)
+        people = len(handRectangles)
+        self.mHandKeypoints = [np.zeros((people, HAND_NUMBER_PARTS, 3), np.float32) for _ in range(2)]
+        want_heat = bool(self.mHeatMapTypes)
+        if want_heat:
+            self.mHeatMaps = [np.zeros((people, HAND_NUMBER_PARTS, self.mNetOutputSize[1], self.mNetOutputSize[0]),
+                                       np.float32) for _ in range(2)]
+        n_scales, rng = self.mMultiScaleNumberAndRange
+        jobs, crops = [], []          # job = (hand, person, scale index, affine)
+        for hand in range(2):
+            mirror = hand == 0
+            for person in range(people):
+                r = tuple(float(v) for v in handRectangles[person][hand])
+                if r[2] != r[3]:
+                    raise Opb200Error("Hand rectangle for hand keypoint estimation must be squared, i.e., width = "
+                                      "height (%f vs. %f)." % (r[2], r[3]))
+                if not (min(r[2], r[3]) > 1 and r[2] * r[3] > 10):
+                    continue
+                if n_scales == 1:
+                    scaled = [r]
+                else:
+                    init = np.float32(1.0) - np.float32(rng) / np.float32(2.0)
+                    scaled = []
+                    for i in range(n_scales):
+                        s = init + np.float32(rng) * np.float32(i) / (np.float32(n_scales) - np.float32(1.0))
+                        w = float(positive_int_round(float(np.float32(r[2]) * s)) // 2 * 2)
+                        h = float(positive_int_round(float(np.float32(r[3]) * s)) // 2 * 2)
+                        scaled.append(recenter(r, w, h))
+                for i, rs in enumerate(scaled):
+                    crop, aff = crop_frame(cvInputData, rs, side, self.mNetOutputSize, mirror)
+                    jobs.append((hand, person, i, aff))
+                    crops.append(crop)
+        if not crops:
+            return
+        peaks = self._net.run(np.stack(crops))
+        best = {}
+        for j, (hand, person, i, aff) in enumerate(jobs):
+            est = connect_keypoints(peaks[j], aff)
+            cur = self.mHandKeypoints[hand][person]
+            if i == 0 or get_average_score(est) > get_average_score(cur):
+                self.mHandKeypoints[hand][person] = est
+            best[(hand, person)] = j        # the reference stores the heat-maps of the LAST scale processed
+        if want_heat:
+            for (hand, person), j in best.items():
+                self.mHeatMaps[hand][person] = _heat_maps_for_person(self._net.heat[j], HAND_NUMBER_PARTS,
+                                                                     self.mHeatMapScaleMode)
+
+
+class FaceExtractorB200:
+    def __init__(self, netInputSize: Tuple[int, int], netOutputSize: Tuple[int, int], caffeProto: str,
+                 caffeTrainedModel: str, gpuId: int = 0, heatMapTypes: Sequence[HeatMapType] = (),
+                 heatMapScaleMode: ScaleMode = ScaleMode.ZeroToOneFixedAspect):
+        if tuple(netInputSize) != tuple(netOutputSize):
+            raise Opb200Error("Net input and output size must be equal.")
+        self.mNetOutputSize = (int(netOutputSize[0]), int(netOutputSize[1]))
+        self.mHeatMapTypes, self.mHeatMapScaleMode = list(heatMapTypes), ScaleMode(heatMapScaleMode)
+        self._net = _CropNet(caffeProto, caffeTrainedModel, gpuId, FACE_CCN_DECREASE_FACTOR)
+        self.mFaceKeypoints = np.zeros((0, FACE_NUMBER_PARTS, 3), np.float32)
+        self.mHeatMaps: Optional[np.ndarray] = None
+        self.mEnabled = True
+
+    def initializationOnThread(self) -> None:
+        self._net.init()
+
+    def getFaceKeypoints(self) -> np.ndarray:
+        return self.mFaceKeypoints
+
+    def getHeatMaps(self) -> Optional[np.ndarray]:
+        return self.mHeatMaps
+
+    def forwardPass(self, faceRectangles: Sequence[Rect], cvInputData: np.ndarray) -> None:
+        if not self.mEnabled or len(faceRectangles) == 0:
+            self.mFaceKeypoints = np.zeros((0, FACE_NUMBER_PARTS, 3), np.float32)
+            return
+        if cvInputData is None or cvInputData.size == 0:
+            raise Opb200Error("Empty cvInputData.")
+        import cv2
+        side = min(self.mNetOutputSize)
+        people = len(faceRectangles)
+        self.mFaceKeypoints = np.zeros((people, FACE_NUMBER_PARTS, 3), np.float32)
+        want_heat = bool(self.mHeatMapTypes)
+        if want_heat:
+            self.mHeatMaps = np.zeros((people, FACE_NUMBER_PARTS, self.mNetOutputSize[1], self.mNetOutputSize[0]),
+                                      np.float32)
+        jobs, crops = [], []
+        for person in range(people):
+            r = tuple(float(v) for v in faceRectangles[person])
+            if r[2] != r[3]:
+                raise Opb200Error("Face rectangle for face keypoint estimation must be squared, i.e., width = "
+                                  "height (%f vs. %f)." % (r[2], r[3]))
+            if not min(r[2], r[3]) > 40:          # only faces with a minimum pixel area
+                continue
+            scale_face = float(np.float32(max(r[2], r[3]))) / float(side)     # float / double
+            m = np.eye(2, 3, dtype=np.float64)
+            m[0, 0] = m[1, 1] = scale_face
+            m[0, 2], m[1, 2] = float(np.float32(r[0])), float(np.float32(r[1]))
+            img = cv2.warpAffine(cvInputData, m, self.mNetOutputSize, flags=cv2.INTER_LINEAR | cv2.WARP_INVERSE_MAP,
+                                 borderMode=cv2.BORDER_CONSTANT, borderValue=(0, 0, 0))
+            jobs.append((person, m))
+            crops.append(u_char_to_float(img))
+        if not crops:
+            return
+        peaks = self._net.run(np.stack(crops))
+        for j, (person, m) in enumerate(jobs):
+            self.mFaceKeypoints[person] = connect_keypoints(peaks[j], m)
+            if want_heat:
+                self.mHeatMaps[person] = _heat_maps_for_person(self._net.heat[j], FACE_NUMBER_PARTS,
+                                                               self.mHeatMapScaleMode)
