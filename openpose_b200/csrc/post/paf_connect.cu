@@ -1,5 +1,7 @@
 // bodyPartConnector on the device: PAF line-integral scores, per-limb sort + greedy one-to-one matching,
-// person assembly, threshold filtering and output arrays -- CPU_ONLY-build semantics, bit-exact.
+// person assembly, threshold filtering and output arrays -- bit-exact in both of the reference's semantics:
+// the CPU_ONLY build (default) and the CUDA build (OPB200_SEMANTICS_CUDA: pafPtrIntoVector +
+// pafVectorIntoPeopleVector, bodyPartConnectorBase.cpp:475-718, see assembleCudaKernel below).
 //
 // Replaces op::connectBodyPartsCpu / op::connectBodyPartsGpu (reference:
 // src/openpose/net/bodyPartConnectorBase.cpp:12-75 getScoreAB, :157-472 createPeopleVector,
@@ -15,6 +17,7 @@
 //                   parallel and only the append order is serialised with a prefix sum.
 // Float arithmetic mirrors the reference's evaluation order with FMA contraction disabled.
 #include "../common.cuh"
+#include <algorithm>
 
 namespace opb
 {
@@ -529,6 +532,276 @@ namespace opb
             c.outCount[n] = written;
     }
 
+    // ------------------------------------------------------------------------------------------------
+    // Kernel C: CUDA-build semantics of the assembly (pafPtrIntoVector :475-542 + pafVectorIntoPeopleVector
+    // :545-718), fed by the score cube of pafCubeKernel<CUDA>. One block per frame:
+    //   1. every cube cell with score > 1e-6 becomes a connection keyed by the reference's tuple
+    //      (total = paf + 0.1*scoreA + 0.1*scoreB, paf, limb, indexA, indexB) packed into 128 bits;
+    //   2. ONE descending sort over all limbs (bitonic; in shared memory up to kCudaSortSmem keys, else in the
+    //      global scratch -- slow but exact for pathological maps);
+    //   3. the five-case assignment walked in order by the whole block in lock-step (state in shared memory,
+    //      people rows hold the reference's flat peak index, merging two people re-labels `assigned` in parallel);
+    //   4. the same filter and output as the CPU-semantics kernel, skipping merged-away people.
+    // ------------------------------------------------------------------------------------------------
+    constexpr int kCudaSortSmem = 4096;
+    struct ConnKey
+    {
+        unsigned long long hi, lo;   // hi = ord(total) << 32 | ord(paf); lo = limb << 16 | indexA << 8 | indexB
+    };
+    __device__ __forceinline__ bool keyLess(const ConnKey& a, const ConnKey& b)
+    {
+        return a.hi < b.hi || (a.hi == b.hi && a.lo < b.lo);
+    }
+    __device__ __forceinline__ unsigned ordFloat(float f)   // monotone float -> unsigned
+    {
+        const unsigned u = __float_as_uint(f);
+        return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+    }
+    __device__ __forceinline__ float unordFloat(unsigned u)
+    {
+        return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+    }
+    // descending bitonic sort of n = 2^k keys by the whole block
+    __device__ void bitonicSortDesc(ConnKey* keys, int n)
+    {
+        for (int size = 2; size <= n; size <<= 1)
+            for (int stride = size >> 1; stride > 0; stride >>= 1)
+            {
+                for (int t = threadIdx.x; t < (n >> 1); t += kAsmThreads)
+                {
+                    const int lo = 2 * t - (t & (stride - 1));
+                    const int hi = lo + stride;
+                    const bool descending = (lo & size) == 0;
+                    const ConnKey a = keys[lo], b = keys[hi];
+                    if (keyLess(a, b) == descending)
+                    {
+                        keys[lo] = b;
+                        keys[hi] = a;
+                    }
+                }
+                __syncthreads();
+            }
+    }
+
+    __global__ void __launch_bounds__(kAsmThreads) assembleCudaKernel(const ConnectArgs c, ConnKey* keysAll,
+                                                                      size_t keysPerFrame)
+    {
+        extern __shared__ __align__(16) unsigned char smraw[];
+        __shared__ int warpSums[kAsmThreads / 32];
+        __shared__ int nKeysS, nPeopleS;
+        const int n = blockIdx.x;
+        const int parts = c.t.parts, pairs = c.t.pairs, mp = c.maxPeaks, po = 3 * (mp + 1);
+        const float* pk = c.peaks + (size_t)n * parts * po;
+        const float* cube = c.cube + (size_t)n * pairs * mp * mp;
+        ConnKey* keys = keysAll + (size_t)n * keysPerFrame;
+
+        // ---- 1. gather ----
+        if (threadIdx.x == 0)
+            nKeysS = 0;
+        __syncthreads();
+        for (int pair = 0; pair < pairs; pair++)
+        {
+            const int partA = c.t.pairTable[2 * pair], partB = c.t.pairTable[2 * pair + 1];
+            const int nA = posIntRound(pk[partA * po]), nB = posIntRound(pk[partB * po]);
+            for (int t = threadIdx.x; t < nA * nB; t += kAsmThreads)
+            {
+                const int a = t / nB, b = t - a * nB;
+                const float s = cube[((size_t)pair * mp + a) * mp + b];
+                if ((double)s > 1e-6)
+                {
+                    const float sA = pk[partA * po + (a + 1) * 3 + 2], sB = pk[partB * po + (b + 1) * 3 + 2];
+                    const float total = add(add(s, mul(0.1f, sA)), mul(0.1f, sB));
+                    ConnKey k;
+                    k.hi = ((unsigned long long)ordFloat(total) << 32) | ordFloat(s);
+                    k.lo = ((unsigned long long)pair << 16) | ((unsigned long long)(a + 1) << 8) | (unsigned)(b + 1);
+                    keys[atomicAdd(&nKeysS, 1)] = k;
+                }
+            }
+        }
+        __syncthreads();
+        const int nKeys = nKeysS;
+
+        // ---- 2. one descending sort over all limbs (keys are unique: ties cannot reorder) ----
+        int sortN = 1;
+        while (sortN < nKeys)
+            sortN <<= 1;
+        if (nKeys > 1)
+        {
+            const ConnKey zero = {0ull, 0ull};            // sorts last
+            if (sortN <= kCudaSortSmem)
+            {
+                ConnKey* sk = reinterpret_cast<ConnKey*>(smraw);
+                for (int t = threadIdx.x; t < sortN; t += kAsmThreads)
+                    sk[t] = t < nKeys ? keys[t] : zero;
+                __syncthreads();
+                bitonicSortDesc(sk, sortN);
+                for (int t = threadIdx.x; t < nKeys; t += kAsmThreads)
+                    keys[t] = sk[t];
+            }
+            else
+            {
+                for (int t = nKeys + threadIdx.x; t < sortN; t += kAsmThreads)
+                    keys[t] = zero;
+                __syncthreads();
+                bitonicSortDesc(keys, sortN);
+            }
+        }
+        __syncthreads();
+
+        // ---- 3. assignment ----
+        const int cap = c.maxPeople;                       // people slots (each new person consumes two free peaks)
+        float* score = reinterpret_cast<float*>(smraw);                           // [cap]
+        unsigned short* rows = reinterpret_cast<unsigned short*>(score + cap);    // [cap][parts] flat peak index
+        short* assigned = reinterpret_cast<short*>(rows + (size_t)cap * parts);   // [parts][mp] person or -1
+        unsigned char* cnt = reinterpret_cast<unsigned char*>(assigned + parts * mp);   // [cap]
+        unsigned char* dead = cnt + cap;                                          // [cap]
+        for (int i = threadIdx.x; i < cap * parts; i += kAsmThreads)
+            rows[i] = 0;
+        for (int i = threadIdx.x; i < parts * mp; i += kAsmThreads)
+            assigned[i] = -1;
+        for (int i = threadIdx.x; i < cap; i += kAsmThreads)
+        {
+            score[i] = 0.f;
+            cnt[i] = 0;
+            dead[i] = 0;
+        }
+        if (threadIdx.x == 0)
+            nPeopleS = 0;
+        __syncthreads();
+        for (int k = 0; k < nKeys; k++)
+        {
+            // every thread reads the same state, takes the same branch; designated threads write; one barrier
+            const ConnKey key = keys[k];
+            const int pair = (int)(key.lo >> 16), ia = (int)((key.lo >> 8) & 0xff), ib = (int)(key.lo & 0xff);
+            const float paf = unordFloat((unsigned)(key.hi & 0xffffffffu));
+            const int partA = c.t.pairTable[2 * pair], partB = c.t.pairTable[2 * pair + 1];
+            const int idxA = (partA * (mp + 1) + ia) * 3 + 2, idxB = (partB * (mp + 1) + ib) * 3 + 2;
+            const int sa = partA * mp + ia - 1, sb = partB * mp + ib - 1;
+            const int aAs = assigned[sa], bAs = assigned[sb];
+            const int nPeople = nPeopleS;
+            if (aAs < 0 && bAs < 0)
+            {
+                __syncthreads();                           // everybody has read nPeopleS / assigned
+                if (nPeople < cap)
+                {
+                    if ((int)threadIdx.x < parts)
+                        rows[nPeople * parts + threadIdx.x] =
+                            (unsigned short)((int)threadIdx.x == partA ? idxA : ((int)threadIdx.x == partB ? idxB : 0));
+                    if (threadIdx.x == 0)
+                    {
+                        cnt[nPeople] = 2;
+                        score[nPeople] = add(add(pk[idxA], pk[idxB]), paf);
+                        assigned[sa] = (short)nPeople;
+                        assigned[sb] = (short)nPeople;
+                        nPeopleS = nPeople + 1;
+                    }
+                }
+            }
+            else if ((aAs >= 0) != (bAs >= 0))
+            {
+                const int have = aAs >= 0 ? aAs : bAs;
+                const int part2 = aAs >= 0 ? partB : partA, idx2 = aAs >= 0 ? idxB : idxA;
+                const bool freeSlot = rows[have * parts + part2] == 0;
+                __syncthreads();
+                if (freeSlot && threadIdx.x == 0)
+                {
+                    rows[have * parts + part2] = (unsigned short)idx2;
+                    cnt[have] = (unsigned char)(cnt[have] + 1);
+                    score[have] = add(score[have], add(pk[idx2], paf));
+                    assigned[aAs >= 0 ? sb : sa] = (short)have;
+                }
+            }
+            else if (aAs == bAs)
+            {
+                __syncthreads();
+                if (threadIdx.x == 0)
+                    score[aAs] = add(score[aAs], paf);
+            }
+            else
+            {
+                const int a1 = min(aAs, bAs), a2 = max(aAs, bAs);
+                const bool clash = (int)threadIdx.x < parts && rows[a1 * parts + threadIdx.x] > 0 &&
+                                   rows[a2 * parts + threadIdx.x] > 0;
+                if (!__syncthreads_or(clash ? 1 : 0))      // complementary: the two people share no body part
+                {
+                    if ((int)threadIdx.x < parts && rows[a1 * parts + threadIdx.x] == 0)
+                        rows[a1 * parts + threadIdx.x] = rows[a2 * parts + threadIdx.x];
+                    if (threadIdx.x == 0)
+                    {
+                        cnt[a1] = (unsigned char)(cnt[a1] + cnt[a2]);
+                        score[a1] = add(score[a1], add(score[a2], paf));
+                        dead[a2] = 1;                      // erased after the loop in the reference (:707-709)
+                    }
+                    for (int i = threadIdx.x; i < parts * mp; i += kAsmThreads)
+                        if (assigned[i] == a2)
+                            assigned[i] = (short)a1;
+                }
+            }
+            __syncthreads();
+        }
+
+        // ---- 4. filter (reference :721-884) + ordered output (reference :887-934) ----
+        const int nPeople = nPeopleS;
+        const float inv = divf(1.f, (float)(parts + pairs));
+        float* outKp = c.outKeypoints + (size_t)n * c.capacity * parts * 3;
+        float* outSc = c.outScores + (size_t)n * c.capacity;
+        int written = 0;
+        for (int attempt = c.maximizePositives ? 1 : 0; attempt < 2; attempt++)
+        {
+            const bool maxPos = attempt == 1;
+            written = 0;
+            for (int base = 0; base < nPeople; base += kAsmThreads) // block-uniform trip count
+            {
+                const int q = base + threadIdx.x;
+                int valid = 0;
+                if (q < nPeople && !dead[q])
+                {
+                    int counter = cnt[q];
+                    bool skip = false;
+                    if (!maxPos && parts == 25)
+                    {
+                        int feet = 0;
+                        for (int p = 19; p < 25; p++)
+                            feet += rows[q * parts + p] > 0;
+                        const int before = counter;
+                        counter -= feet;
+                        skip = counter != before && counter <= 4;
+                    }
+                    valid = !skip && counter >= c.minSubsetCnt
+                            && divf(score[q], (float)counter) >= c.minSubsetScore;
+                }
+                int total = 0;
+                const int slot = written + blockExclusiveScan(valid, warpSums, total);
+                if (valid && slot < c.capacity)
+                {
+                    for (int p = 0; p < parts; p++)
+                    {
+                        const int idx = rows[q * parts + p];
+                        float* o = outKp + ((size_t)slot * parts + p) * 3;
+                        if (idx > 0)
+                        {
+                            o[0] = mul(pk[idx - 2], c.scale);
+                            o[1] = mul(pk[idx - 1], c.scale);
+                            o[2] = pk[idx];
+                        }
+                        else
+                        {
+                            o[0] = 0.f;
+                            o[1] = 0.f;
+                            o[2] = 0.f;
+                        }
+                    }
+                    outSc[slot] = mul(score[q], inv);
+                }
+                written += total;
+            }
+            if (written > 0)
+                break;
+        }
+        if (threadIdx.x == 0)
+            c.outCount[n] = written;
+    }
+
     static opb200_status fillArgs(ConnectArgs& c, const opb200_connect_params* p, const int heat_shape[4])
     {
         OPB_REQUIRE(p != nullptr && heat_shape != nullptr, "connector: null argument");
@@ -570,6 +843,15 @@ extern "C" size_t opb200_connect_scratch_bytes(const opb200_connect_params* p, i
     const opb::ModelTables* t = opb::tablesFor(p->pose_model);
     if (!t)
         return 0;
+    if (p->semantics == OPB200_SEMANTICS_CUDA)
+    {
+        // score cube + the connection keys of every cube cell, rounded up to a power of two for the sort
+        const size_t cells = (size_t)t->pairs * p->max_peaks * p->max_peaks;
+        size_t keys = 1;
+        while (keys < cells)
+            keys <<= 1;
+        return (size_t)n_frames * (sizeof(float) * cells + sizeof(opb::ConnKey) * keys) + 256;
+    }
     return sizeof(int) * (size_t)n_frames * t->pairs * (1 + 3 * (size_t)p->max_peaks);
 }
 
@@ -606,11 +888,6 @@ extern "C" opb200_status opb200_connect(float* out_keypoints, float* out_scores,
     const opb200_status s = fillArgs(c, p, heat_shape);
     if (s != OPB200_OK)
         return s;
-    if (p->semantics != OPB200_SEMANTICS_CPU)
-    {
-        setError("connector: only OPB200_SEMANTICS_CPU assembly (createPeopleVector) is implemented on the device");
-        return OPB200_ERR_UNSUPPORTED;
-    }
     c.heat = heat;
     c.peaks = peaks;
     c.cube = nullptr;
@@ -622,6 +899,29 @@ extern "C" opb200_status opb200_connect(float* out_keypoints, float* out_scores,
     const int nFrames = heat_shape[0];
     OPB_REQUIRE(nFrames <= 65535, "connector: too many frames for one launch");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (p->semantics == OPB200_SEMANTICS_CUDA)
+    {
+        // CUDA-build semantics: CUDA-rule score cube -> global sort over all limbs -> five-case assignment
+        const size_t cells = (size_t)c.t.pairs * c.maxPeaks * c.maxPeaks;
+        size_t keysPerFrame = 1;
+        while (keysPerFrame < cells)
+            keysPerFrame <<= 1;
+        c.cube = static_cast<float*>(scratch);
+        const size_t cubeBytes = (sizeof(float) * cells * nFrames + 255) & ~(size_t)255;
+        ConnKey* keys = reinterpret_cast<ConnKey*>(static_cast<unsigned char*>(scratch) + cubeBytes);
+        const dim3 grid((c.maxPeaks * c.maxPeaks + 255) / 256, c.t.pairs, nFrames);
+        pafCubeKernel<OPB200_SEMANTICS_CUDA><<<grid, 256, 0, st>>>(c);
+        OPB_LAUNCH_CHECK();
+        c.maxPeople = (c.t.parts * c.maxPeaks / 2 + 4) / 4 * 4;   // a new person takes two unassigned peaks
+        const size_t state = sizeof(float) * c.maxPeople + sizeof(unsigned short) * (size_t)c.maxPeople * c.t.parts +
+                             sizeof(short) * (size_t)c.t.parts * c.maxPeaks + 2 * (size_t)c.maxPeople;
+        const size_t smemC = std::max(state, sizeof(ConnKey) * (size_t)kCudaSortSmem);
+        OPB_REQUIRE(smemC <= 200 * 1024, "connector: max_peaks too large for the CUDA-semantics assembly");
+        OPB_CUDA(cudaFuncSetAttribute(assembleCudaKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemC));
+        assembleCudaKernel<<<nFrames, kAsmThreads, smemC, st>>>(c, keys, keysPerFrame);
+        OPB_LAUNCH_CHECK();
+        return OPB200_OK;
+    }
 
     const size_t smemA = sizeof(unsigned long long) * (size_t)c.sortCap;
     OPB_CUDA(cudaFuncSetAttribute(pafMatchKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemA));

@@ -73,6 +73,47 @@ def test_connect_matches_oracle(port, cuda, case):
         assert np.array_equal(cube, port.pair_scores(maps, peaks, model, mode=mode))
 
 
+@pytest.mark.parametrize("case", POST_CASES, ids=case_id)
+def test_connect_cuda_semantics_matches_reference(port, cuda, case):
+    """CUDA-build path: CUDA-rule score cube -> pafPtrIntoVector (one global sort) -> pafVectorIntoPeopleVector
+    (five-case assignment incl. merging) -> filter -> arrays; against the reference's own object code when
+    oracle/_ref is built, else the C restatement (tests/test_oracle_vs_ref.py keeps the two bit-equal)."""
+    from oracle.post import Ref
+    impl = Ref() if Ref.available() else port
+    model = case[0]
+    parts = model_dims(model)[0]
+    maps, _ = make_case(case)
+    peaks = port.nms(maps, 0.05, parts, off=(0.25, 0.25))
+    heat_d = torch.from_numpy(maps[None]).to(cuda)
+    peaks_d = torch.from_numpy(peaks[None]).to(cuda)
+    from oracle.post import pose_defaults
+    for mp in (False, True):
+        cube = port.pair_scores(maps, peaks, model, p=pose_defaults(model, mp), mode=MODE_CUDA)
+        want = impl.connect_from_pair_scores(cube, peaks, model, scale=1.959, maximize_positives=mp)
+        kp, sc = want[0], want[1]
+        params = post.make_connect_params(model, scale_factor=1.959, maximize_positives=mp, semantics=MODE_CUDA)
+        gk, gs, gc = post.connect_body_parts_gpu(heat_d, peaks_d, params, capacity=1024)
+        n = int(gc[0].item())
+        assert n == kp.shape[0], (n, kp.shape)
+        assert np.array_equal(gk[0, :n].cpu().numpy(), kp)
+        assert np.array_equal(gs[0, :n].cpu().numpy(), sc)
+
+
+def test_connect_cuda_semantics_batch(port, cuda):
+    cases = [POST_CASES[1], POST_CASES[5], POST_CASES[3]]
+    maps = np.stack([make_case(c)[0] for c in cases])
+    peaks = np.stack([port.nms(m, 0.05, 25, off=(0.25, 0.25)) for m in maps])
+    params = post.make_connect_params(0, scale_factor=2.0, semantics=MODE_CUDA)
+    gk, gs, gc = post.connect_body_parts_gpu(torch.from_numpy(maps).to(cuda), torch.from_numpy(peaks).to(cuda),
+                                             params, capacity=256)
+    for i in range(len(cases)):
+        cube = port.pair_scores(maps[i], peaks[i], 0, mode=MODE_CUDA)
+        kp, sc = port.connect_from_pair_scores(cube, peaks[i], 0, scale=2.0)[:2]
+        n = int(gc[i].item())
+        assert n == kp.shape[0]
+        assert np.array_equal(gk[i, :n].cpu().numpy(), kp) and np.array_equal(gs[i, :n].cpu().numpy(), sc)
+
+
 def test_connect_batch_of_frames(port, cuda):
     cases = [POST_CASES[1], POST_CASES[2], POST_CASES[5], POST_CASES[0]]
     maps = np.stack([make_case(c)[0] for c in cases])
