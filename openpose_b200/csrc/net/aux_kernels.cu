@@ -210,6 +210,10 @@ namespace opb
         bool relu = true;                    // every slope zero: add + max
         for (int i = 0; i < cout; ++i)
             relu = relu && (__ldg(slope + i) == 0.f);
+        float2 biasReg[8];                   // this lane's two output channels of every n-tile
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt)
+            biasReg[nt] = nt < nTiles ? __ldg(reinterpret_cast<const float2*>(bias) + nt * 4 + q) : make_float2(0.f, 0.f);
         // work unit = 32 consecutive pixels of one image row: no per-pixel division, and a unit away from the image
         // border gathers its patches without any bounds test
         const int xBlocks = (W + 31) >> 5;
@@ -260,8 +264,8 @@ namespace opb
             {
                 if (nt >= nTiles)
                     break;
-                const float2 b2 = __ldg(reinterpret_cast<const float2*>(bias) + nt * 4 + q);
-                const float2 s2 = __ldg(reinterpret_cast<const float2*>(slope) + nt * 4 + q);
+                const float2 b2 = biasReg[nt];
+                const float2 s2 = relu ? make_float2(0.f, 0.f) : __ldg(reinterpret_cast<const float2*>(slope) + nt * 4 + q);
 #pragma unroll
                 for (int t = 0; t < 2; ++t)
                 {
@@ -293,13 +297,28 @@ namespace opb
             }
             __syncwarp();
             // 32 pixels x nTiles 16-byte chunks, written so that a pixel's channels are contiguous in global memory
-            const int chunks = 32 * nTiles;
-            for (int i = lane; i < chunks; i += 32)
+            if (nTiles == 8)
             {
-                const int px = i / nTiles, ch = i - px * nTiles;
-                if (x0 + px < W)
-                    *reinterpret_cast<uint4*>(dst + (p0 + px) * dstStride + ch * 8) =
-                        *reinterpret_cast<const uint4*>(st + px * kFirstPitch + ch * 16);
+                // 64 channels: lane = (pixel & 3, chunk), 8 unrolled stores of 4 pixels x 128 contiguous bytes each
+                const int ch = lane & 7, pxBase = lane >> 3;
+                __nv_bfloat16* o = dst + (p0 + pxBase) * dstStride + ch * 8;
+                const uint8_t* sp = st + pxBase * kFirstPitch + ch * 16;
+#pragma unroll
+                for (int it = 0; it < 8; ++it)
+                    if (x0 + pxBase + 4 * it < W)
+                        *reinterpret_cast<uint4*>(o + (long long)(4 * it) * dstStride) =
+                            *reinterpret_cast<const uint4*>(sp + 4 * it * kFirstPitch);
+            }
+            else
+            {
+                const int chunks = 32 * nTiles;
+                for (int i = lane; i < chunks; i += 32)
+                {
+                    const int px = i / nTiles, ch = i - px * nTiles;
+                    if (x0 + px < W)
+                        *reinterpret_cast<uint4*>(dst + (p0 + px) * dstStride + ch * 8) =
+                            *reinterpret_cast<const uint4*>(st + px * kFirstPitch + ch * 16);
+                }
             }
             __syncwarp();
         }

@@ -457,7 +457,17 @@ namespace opb
     {
         using Cfg = ConvCfg<BN>;
         const int aStage = 2 * convTileBytes(k, kxSpan);
-        bStages = (BN <= 64 || kxSpan > 1) ? 6 : 4;
+        // weight stages: as many as fit next to two activation stages, up to `want` (one weight stage is only
+        // 8 MMAs of tensor time, so the stream needs depth to cover the TMA round trip)
+        int want = (kxSpan > 1 || BN <= 64) ? 6 : 4;
+        if (const char* e = std::getenv("OPB200_BSTAGES"))
+            want = std::atoi(e);
+        const int fitB = (kSmemLimit - (Cfg::kStagingBytes + kAuxBytes + 1024) - 2 * aStage) / Cfg::kBBytes;
+        bStages = want < fitB ? want : fitB;
+        if (bStages > kMaxBStages)
+            bStages = kMaxBStages;
+        if (bStages < 2)
+            return false;
         resident = 0;
         if (singleNTile && bStagesAll <= kMaxBStages &&
             Cfg::kStagingBytes + kAuxBytes + 1024 + bStagesAll * Cfg::kBBytes + 2 * aStage <= kSmemLimit)

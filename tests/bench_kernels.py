@@ -1,0 +1,35 @@
+"""Debug tool: device-time of single post-processing kernels at given shapes (CUDA events, L2-cold inputs)."""
+import sys
+import torch
+from openpose_b200 import post
+
+
+def timeit(fn, reps=20):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps
+
+
+def main():
+    dev = torch.device("cuda:0")
+    for name, n, c in (("hand", 64, 22), ("face", 32, 71)):
+        src = torch.rand((n, c, 368, 368), device=dev)
+        dst = torch.empty((n, 1, c - 1, 3), device=dev)
+        ms = timeit(lambda: post.maximum_gpu(dst, src))
+        gb = n * (c - 1) * 368 * 368 * 4 / 1e9
+        print("maximum %s x%d: %.3f ms  %.0f GB/s" % (name, n, ms, gb / ms * 1e3))
+        small = torch.rand((n, c, 46, 46), device=dev)
+        ms = timeit(lambda: post.resize_and_merge_gpu(src, [small]))
+        gb = n * c * (368 * 368 + 46 * 46) * 4 / 1e9
+        print("resize x8 %s x%d: %.3f ms  %.0f GB/s" % (name, n, ms, gb / ms * 1e3))
+
+
+if __name__ == "__main__":
+    main()
