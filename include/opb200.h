@@ -80,6 +80,30 @@ opb200_status opb200_maximum(float* target, void* scratch, const float* source, 
                              const int source_shape[4], void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
+ * Frame pre-processing -- replaces the device branch of op::CvMatToOpInput::createArray
+ * (reference: src/openpose/core/cvMatToOpInput.cpp:108-148): op::reorderAndNormalize
+ * (include/openpose/gpu/cuda.hpp, src/openpose/gpu/cuda.cu:11-25,69-83) followed by op::resizeAndPadRbgGpu
+ * (include/openpose/net/resizeAndMergeBase.hpp, src/openpose/net/resizeAndMergeBase.cu:56-78,531-551), as one
+ * kernel without the float scratch frame. src: n_frames BGR frames (N,Hs,Ws,3) u8 on the device;
+ * dst: (N,3,Ht,Wt) fp32 = bicubic sample of (v/256 - 0.5) at ((x+0.5)/scale-0.5, (y+0.5)/scale-0.5) inside
+ * [0,Ws*scale) x [0,Hs*scale), 0 elsewhere -- the net input op::Net::forwardPass / opb200_net_forward takes.
+ * ------------------------------------------------------------------------------------------------- */
+opb200_status opb200_preprocess(float* dst, const unsigned char* src, int n_frames, int src_h, int src_w,
+                                int dst_h, int dst_w, float scale, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Hand / face crops -- replaces cv::warpAffine(INTER_LINEAR | WARP_INVERSE_MAP, BORDER_CONSTANT 0) +
+ * op::uCharCvMatToFloatPtr(normalize = 1) in HandExtractorCaffe cropFrame (reference:
+ * src/openpose/hand/handExtractorCaffe.cpp:44-76) and FaceExtractorCaffe::forwardPass
+ * (src/openpose/face/faceExtractorCaffe.cpp:133-149; src/openpose/utilities/openCv.cpp:57-130).
+ * frame: one BGR frame (Hs,Ws,3) u8 on the device; matrices: n_crops 2x3 row-major double inverse maps (crop pixel
+ * -> frame position; the cv::Mat the reference builds) on the device; dst (n_crops,3,Ht,Wt) fp32 = v/256 - 0.5 of
+ * OpenCV's 8-bit fixed-point bilinear sample. All crops of a frame in one launch.
+ * ------------------------------------------------------------------------------------------------- */
+opb200_status opb200_crop_warp(float* dst, const unsigned char* frame, const double* matrices, int n_crops,
+                               int src_h, int src_w, int dst_h, int dst_w, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
  * bodyPartConnector -- replaces op::connectBodyPartsGpu<float> / op::connectBodyPartsCpu<float>
  * (reference: include/openpose/net/bodyPartConnectorBase.hpp:8-24, src/openpose/net/bodyPartConnectorBase.cpp:
  * 12-75 getScoreAB, 157-472 createPeopleVector, 721-884 filter, 887-934 output; .cu:15-66,108-145 scores).

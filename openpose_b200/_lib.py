@@ -42,6 +42,10 @@ SYMBOLS = {
                              C.c_int, C.c_void_p]),
     "opb200_maximum_scratch_bytes": (C.c_size_t, [_I4, _I4]),
     "opb200_maximum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, _I4, _I4, C.c_void_p]),
+    "opb200_preprocess": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                    C.c_float, C.c_void_p]),
+    "opb200_crop_warp": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                   C.c_void_p]),
     "opb200_connect_scratch_bytes": (C.c_size_t, [C.POINTER(ConnectParams), C.c_int]),
     "opb200_connect": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                  C.c_void_p, _I4, C.POINTER(ConnectParams), C.c_void_p]),

@@ -3,7 +3,7 @@ crop -> net -> resizeAndMerge x8 -> maximum -> affine back-projection.
 
 Mirrors (reference files relative to zengjianping/openpose, same argument meaning / error text):
   HandExtractorB200.forwardPass <- HandExtractorCaffe::forwardPass  src/openpose/hand/handExtractorCaffe.cpp:305-464
-      crop_frame                <- cropFrame                        handExtractorCaffe.cpp:44-76
+      crop_matrix + crop_frames_gpu <- cropFrame                    handExtractorCaffe.cpp:44-76
       connect_keypoints         <- connectKeypoints                 handExtractorCaffe.cpp:78-102
   FaceExtractorB200.forwardPass <- FaceExtractorCaffe::forwardPass  src/openpose/face/faceExtractorCaffe.cpp:175-300
   get_average_score             <- getAverageScore                  src/openpose/utilities/keypoint.cpp:352-373
@@ -12,8 +12,9 @@ Mirrors (reference files relative to zengjianping/openpose, same argument meanin
 B200-first difference (results per crop are the reference's): the reference runs its net once per crop, batch 1,
 one after the other; here every valid crop of the frame (both hands of every person, every scale) goes through
 ONE batched net forward, one resize launch and one maximum launch -- the unit SURVEY 8(e) shards across GPUs.
-The crop itself (cv::warpAffine, INTER_LINEAR | WARP_INVERSE_MAP) stays on the host as in the reference
-(SURVEY 8(f) rank 1 moves it to the device).
+The frame is uploaded once as u8 and the crops themselves (cv::warpAffine INTER_LINEAR | WARP_INVERSE_MAP +
+uCharCvMatToFloatPtr in the reference, on the host, one crop at a time) are cut on the device by one launch of
+opb200_crop_warp, bit-identical to OpenCV's 8-bit fixed-point result.
 """
 from __future__ import annotations
 
@@ -22,6 +23,7 @@ from typing import List, Optional, Sequence, Tuple
 import numpy as np
 import torch
 
+from . import _lib
 from . import net as netmod
 from . import post
 from ._lib import Opb200Error
@@ -41,20 +43,40 @@ def u_char_to_float(image_hwc: np.ndarray) -> np.ndarray:
     return (image_hwc.transpose(2, 0, 1).astype(np.float32) * np.float32(1.0 / 256.0)) - np.float32(0.5)
 
 
-def crop_frame(cv_input: np.ndarray, rect: Rect, net_input_side: int, net_output_size: Tuple[int, int],
-               mirror: bool) -> Tuple[np.ndarray, np.ndarray]:
-    """-> (crop (3,H,W) float32, affine 2x3 float64): crop pixel (u,v) <- image (a00*u + a02, a11*v + a12)."""
-    import cv2
+def crop_matrix(rect: Rect, net_input_side: int, mirror: bool) -> np.ndarray:
+    """The 2x3 CV_64F inverse map cropFrame builds (handExtractorCaffe.cpp:53-68): crop pixel (u,v) <- image
+    (a00*u + a02, a11*v + a12); float arithmetic for the scale and the mirrored offset, as the reference."""
     scale = np.float32(rect[2]) / np.float32(net_input_side)
     m = np.eye(2, 3, dtype=np.float64)
     m[0, 0] = -float(scale) if mirror else float(scale)
     m[1, 1] = float(scale)
     m[0, 2] = float(np.float32(rect[0]) + np.float32(rect[2])) if mirror else float(np.float32(rect[0]))
     m[1, 2] = float(np.float32(rect[1]))
-    img = cv2.warpAffine(cv_input, m, (int(net_output_size[0]), int(net_output_size[1])),
-                         flags=cv2.INTER_LINEAR | cv2.WARP_INVERSE_MAP, borderMode=cv2.BORDER_CONSTANT,
-                         borderValue=(0, 0, 0))
-    return u_char_to_float(img), m
+    return m
+
+
+def upload_frame(cv_input, device) -> torch.Tensor:
+    """(H,W,3) uint8 BGR frame (numpy or torch, host or device) -> contiguous CUDA tensor; one H2D per frame."""
+    if cv_input is None or (cv_input.numel() if isinstance(cv_input, torch.Tensor) else cv_input.size) == 0:
+        raise Opb200Error("Empty cvInputData.")
+    t = cv_input if isinstance(cv_input, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(cv_input))
+    if t.dim() != 3 or t.shape[2] != 3 or t.dtype != torch.uint8:
+        raise Opb200Error("Input images must be 3-channel BGR.")
+    return t.to(device, non_blocking=True).contiguous()
+
+
+def crop_frames_gpu(frame: torch.Tensor, matrices: Sequence[np.ndarray], net_output_size: Tuple[int, int]) -> torch.Tensor:
+    """All crops of one frame in one launch: cv::warpAffine(INTER_LINEAR | WARP_INVERSE_MAP, BORDER_CONSTANT 0) +
+    uCharCvMatToFloatPtr (cropFrame, handExtractorCaffe.cpp:44-76; faceExtractorCaffe.cpp:133-149) ->
+    (N,3,H,W) float32 on the frame's device (libopb200: opb200_crop_warp)."""
+    mats = torch.from_numpy(np.ascontiguousarray(np.stack(matrices), np.float64).reshape(-1, 6)).to(frame.device)
+    out = torch.empty((mats.shape[0], 3, int(net_output_size[1]), int(net_output_size[0])), dtype=torch.float32,
+                      device=frame.device)
+    L = _lib.lib()
+    _lib.check(L.opb200_crop_warp(out.data_ptr(), frame.data_ptr(), mats.data_ptr(), mats.shape[0], frame.shape[0],
+                                  frame.shape[1], out.shape[2], out.shape[3],
+                                  torch.cuda.current_stream(frame.device).cuda_stream))
+    return out
 
 
 def connect_keypoints(peaks: np.ndarray, affine: np.ndarray) -> np.ndarray:
@@ -94,9 +116,9 @@ class _CropNet:
     def init(self) -> None:
         self.net.initializationOnThread()
 
-    def run(self, crops: np.ndarray) -> np.ndarray:
-        """crops (N,3,H,W) float32 -> peaks (N, parts, 3) in crop pixels (host)."""
-        self.net.forwardPass(np.ascontiguousarray(crops, np.float32))
+    def run(self, crops) -> np.ndarray:
+        """crops (N,3,H,W) float32 (CUDA tensor, or numpy) -> peaks (N, parts, 3) in crop pixels (host)."""
+        self.net.forwardPass(crops if isinstance(crops, torch.Tensor) else np.ascontiguousarray(crops, np.float32))
         out = self.net.getOutputBlobArray()
         top = resize_and_merge_top_shape(list(out.shape), self.factor, 1.0, False)
         if self.heat is None or list(self.heat.shape) != top:
@@ -151,7 +173,7 @@ class HandExtractorB200:
             self.mHeatMaps = [np.zeros((people, HAND_NUMBER_PARTS, self.mNetOutputSize[1], self.mNetOutputSize[0]),
                                        np.float32) for _ in range(2)]
         n_scales, rng = self.mMultiScaleNumberAndRange
-        jobs, crops = [], []          # job = (hand, person, scale index, affine)
+        jobs = []                     # job = (hand, person, scale index, affine)
         for hand in range(2):
             mirror = hand == 0
             for person in range(people):
@@ -172,12 +194,11 @@ class HandExtractorB200:
                         h = float(positive_int_round(float(np.float32(r[3]) * s)) // 2 * 2)
                         scaled.append(recenter(r, w, h))
                 for i, rs in enumerate(scaled):
-                    crop, aff = crop_frame(cvInputData, rs, side, self.mNetOutputSize, mirror)
-                    jobs.append((hand, person, i, aff))
-                    crops.append(crop)
-        if not crops:
+                    jobs.append((hand, person, i, crop_matrix(rs, side, mirror)))
+        if not jobs:
             return
-        peaks = self._net.run(np.stack(crops))
+        frame = upload_frame(cvInputData, torch.device("cuda", self._net.gpu))
+        peaks = self._net.run(crop_frames_gpu(frame, [j[3] for j in jobs], self.mNetOutputSize))
         best = {}
         for j, (hand, person, i, aff) in enumerate(jobs):
             est = connect_keypoints(peaks[j], aff)
@@ -219,7 +240,6 @@ class FaceExtractorB200:
             return
         if cvInputData is None or cvInputData.size == 0:
             raise Opb200Error("Empty cvInputData.")
-        import cv2
         side = min(self.mNetOutputSize)
         people = len(faceRectangles)
         self.mFaceKeypoints = np.zeros((people, FACE_NUMBER_PARTS, 3), np.float32)
@@ -227,7 +247,7 @@ class FaceExtractorB200:
         if want_heat:
             self.mHeatMaps = np.zeros((people, FACE_NUMBER_PARTS, self.mNetOutputSize[1], self.mNetOutputSize[0]),
                                       np.float32)
-        jobs, crops = [], []
+        jobs = []
         for person in range(people):
             r = tuple(float(v) for v in faceRectangles[person])
             if r[2] != r[3]:
@@ -239,13 +259,11 @@ class FaceExtractorB200:
             m = np.eye(2, 3, dtype=np.float64)
             m[0, 0] = m[1, 1] = scale_face
             m[0, 2], m[1, 2] = float(np.float32(r[0])), float(np.float32(r[1]))
-            img = cv2.warpAffine(cvInputData, m, self.mNetOutputSize, flags=cv2.INTER_LINEAR | cv2.WARP_INVERSE_MAP,
-                                 borderMode=cv2.BORDER_CONSTANT, borderValue=(0, 0, 0))
             jobs.append((person, m))
-            crops.append(u_char_to_float(img))
-        if not crops:
+        if not jobs:
             return
-        peaks = self._net.run(np.stack(crops))
+        frame = upload_frame(cvInputData, torch.device("cuda", self._net.gpu))
+        peaks = self._net.run(crop_frames_gpu(frame, [j[1] for j in jobs], self.mNetOutputSize))
         for j, (person, m) in enumerate(jobs):
             self.mFaceKeypoints[person] = connect_keypoints(peaks[j], m)
             if want_heat:

@@ -71,6 +71,10 @@ class Port:
                                        C.c_int, C.c_int]
         L.opo_maximum.restype = None
         L.opo_maximum.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int]
+        L.opo_preprocess.restype = C.c_int
+        L.opo_preprocess.argtypes = [_f32p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float]
+        L.opo_crop_warp.restype = None
+        L.opo_crop_warp.argtypes = [_f32p, C.c_void_p, C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int, C.c_int]
         L.opo_pair_scores.restype = None
         L.opo_pair_scores.argtypes = [_f32p, _f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
                                       C.c_float, C.c_float, C.c_int]
@@ -113,6 +117,26 @@ class Port:
         _, h, w = heat.shape
         out = np.empty((parts, 3), np.float32)
         self.lib.opo_maximum(_fp(out), _fp(heat), parts, h, w)
+        return out
+
+    def preprocess(self, frame: np.ndarray, net_size, scale: float) -> np.ndarray:
+        """frame (Hs,Ws,3) u8 BGR -> (3,Ht,Wt) fp32 net input; net_size = (Ht, Wt)."""
+        frame = np.ascontiguousarray(frame, np.uint8)
+        hs, ws, ch = frame.shape
+        assert ch == 3
+        out = np.empty((3, int(net_size[0]), int(net_size[1])), np.float32)
+        rc = self.lib.opo_preprocess(_fp(out), frame.ctypes.data_as(C.c_void_p), hs, ws, out.shape[1],
+                                     out.shape[2], float(scale))
+        assert rc == 0
+        return out
+
+    def crop_warp(self, frame: np.ndarray, matrix: np.ndarray, size) -> np.ndarray:
+        """frame (Hs,Ws,3) u8, matrix 2x3 float64 inverse map, size = (Wt, Ht) as cv::Size -> (3,Ht,Wt) fp32."""
+        frame = np.ascontiguousarray(frame, np.uint8)
+        m = np.ascontiguousarray(matrix, np.float64).reshape(6)
+        out = np.empty((3, int(size[1]), int(size[0])), np.float32)
+        self.lib.opo_crop_warp(_fp(out), frame.ctypes.data_as(C.c_void_p), m.ctypes.data_as(C.POINTER(C.c_double)),
+                               frame.shape[0], frame.shape[1], out.shape[1], out.shape[2])
         return out
 
     def pair_scores(self, heat, peaks, model, p=None, max_peaks=MAX_PEAKS, mode=MODE_CPU) -> np.ndarray:

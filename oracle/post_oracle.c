@@ -190,6 +190,81 @@ void opo_resize_merge(float* dst, const float* const* srcs, const int* hs, const
 }
 
 /* ------------------------------------------------------------------------------------------------
+ * Frame pre-processing, the reference's device path of CvMatToOpInput::createArray
+ * (src/openpose/core/cvMatToOpInput.cpp:108-148): reorderAndNormalize (src/openpose/gpu/cuda.cu:11-25)
+ * into a planar float scratch, then resizeAndPadKernel (src/openpose/net/resizeAndMergeBase.cu:56-78).
+ * The reference only has device code for this (nvcc may contract a*b+c there); the restatement evaluates
+ * the expressions as written, without contraction (-ffp-contract=off), like the rest of this file.
+ * src: (hs, ws, 3) u8; dst: (3, ht, wt). Returns 0, or 1 when the scratch cannot be allocated.
+ * ------------------------------------------------------------------------------------------------ */
+int opo_preprocess(float* dst, const unsigned char* src, int hs, int ws, int ht, int wt, float scale)
+{
+    const size_t area = (size_t)hs * ws;
+    float* planar = (float*)malloc(3 * area * sizeof(float));
+    if (!planar)
+        return 1;
+    for (int c = 0; c < 3; c++)
+        for (size_t i = 0; i < area; i++)
+            planar[c * area + i] = (float)src[i * 3 + c] * (1 / 256.f) - 0.5f;
+    for (int c = 0; c < 3; c++)
+        for (int y = 0; y < ht; y++)
+            for (int x = 0; x < wt; x++)
+            {
+                float v = 0.f;
+                if ((float)x < (float)ws * scale && (float)y < (float)hs * scale)
+                {
+                    const float xs = ((float)x + 0.5f) / scale - 0.5f;
+                    const float ys = ((float)y + 0.5f) / scale - 0.5f;
+                    v = bicubic_at(planar + c * area, xs, ys, ws, hs);
+                }
+                dst[((size_t)c * ht + y) * wt + x] = v;
+            }
+    free(planar);
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Hand / face crop: cv::warpAffine(frame, M, size, INTER_LINEAR | WARP_INVERSE_MAP, BORDER_CONSTANT, 0) +
+ * uCharCvMatToFloatPtr(normalize = 1), as called by src/openpose/hand/handExtractorCaffe.cpp:44-76 and
+ * src/openpose/face/faceExtractorCaffe.cpp:133-149 (src/openpose/utilities/openCv.cpp:57-130: v/256 - 0.5, CHW).
+ * cv::warpAffine lives in OpenCV (a dependency, not vendored in the reference; any 2.4.x-4.x the user installed).
+ * This restates its published 8-bit bilinear algorithm (modules/imgproc/src/imgwarp.cpp: AB_BITS 10, INTER_BITS 5,
+ * INTER_REMAP_COEF_BITS 15, cvRound = round half to even) and is pinned against cv2 4.13.0 (tests/test_crop_cpu.py,
+ * tests/golden/crop_warp.npz). m: the 2x3 inverse map as doubles. frame (hs, ws, 3) u8 -> dst (3, ht, wt).
+ * ------------------------------------------------------------------------------------------------ */
+static int sat_short(int v) { return v < -32768 ? -32768 : (v > 32767 ? 32767 : v); }
+
+void opo_crop_warp(float* dst, const unsigned char* frame, const double* m, int hs, int ws, int ht, int wt)
+{
+    for (int y = 0; y < ht; y++)
+    {
+        const int X0 = (int)lrint((m[1] * y + m[2]) * 1024) + 16;
+        const int Y0 = (int)lrint((m[4] * y + m[5]) * 1024) + 16;
+        for (int x = 0; x < wt; x++)
+        {
+            const int adelta = (int)lrint(m[0] * x * 1024), bdelta = (int)lrint(m[3] * x * 1024);
+            const int X = (X0 + adelta) >> 5, Y = (Y0 + bdelta) >> 5;
+            const int sx = sat_short(X >> 5), sy = sat_short(Y >> 5), fx = X & 31, fy = Y & 31;
+            /* the int16 weight table: saturate_cast<short>(w * 32768) of the float products, which are exact */
+            const int w[4] = {(32 - fy) * (32 - fx) * 32, (32 - fy) * fx * 32, fy * (32 - fx) * 32, fy * fx * 32};
+            for (int c = 0; c < 3; c++)
+            {
+                int acc = 0;
+                for (int k = 0; k < 4; k++)
+                {
+                    const int xx = sx + (k & 1), yy = sy + (k >> 1);
+                    if (xx >= 0 && xx < ws && yy >= 0 && yy < hs)
+                        acc += w[k] * frame[((size_t)yy * ws + xx) * 3 + c];
+                }
+                int v = (acc + (1 << 14)) >> 15;
+                v = v < 0 ? 0 : (v > 255 ? 255 : v);
+                dst[((size_t)c * ht + y) * wt + x] = (float)v * (1 / 256.f) - 0.5f;
+            }
+        }
+    }
+}
+
+/* ------------------------------------------------------------------------------------------------
  * maximum: src/openpose/net/maximumBase.cpp:8-57 (cv::minMaxLoc = first maximum in raster order),
  * src/openpose/net/maximumBase.cu:85-113. target (parts, 3) = (x, y, value); background (last) skipped.
  * ------------------------------------------------------------------------------------------------ */

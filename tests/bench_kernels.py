@@ -2,6 +2,7 @@
 import sys
 import torch
 from openpose_b200 import post
+from openpose_b200.op_input import preprocess_gpu
 
 
 def timeit(fn, reps=20):
@@ -29,6 +30,13 @@ def main():
         ms = timeit(lambda: post.resize_and_merge_gpu(src, [small]))
         gb = n * c * (368 * 368 + 46 * 46) * 4 / 1e9
         print("resize x8 %s x%d: %.3f ms  %.0f GB/s" % (name, n, ms, gb / ms * 1e3))
+    for hs, ws, n in ((1080, 1920, 44), (720, 1280, 44), (480, 640, 44), (368, 656, 44)):
+        frames = torch.randint(0, 256, (n, hs, ws, 3), dtype=torch.uint8, device=dev)
+        dst = torch.empty((n, 3, 368, 656), device=dev)
+        scale = min(655.0 / (ws - 1), 367.0 / (hs - 1))
+        ms = timeit(lambda: preprocess_gpu(dst, frames, scale))
+        gb = n * (hs * ws * 3 + 3 * 368 * 656 * 4) / 1e9
+        print("preprocess %dx%d x%d: %.3f ms  %.0f GB/s" % (ws, hs, n, ms, gb / ms * 1e3))
 
 
 if __name__ == "__main__":

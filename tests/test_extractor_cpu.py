@@ -95,17 +95,18 @@ def test_pose_extractor_sanity_errors():
     assert ex.getHeatMapsCopy().size == 0 and ex.getCandidatesCopy() == []
 
 
-def test_crop_math():
-    cv2 = pytest.importorskip("cv2")
+def test_crop_math(port):
     rng = np.random.default_rng(3)
     img = rng.integers(0, 256, (120, 160, 3), dtype=np.uint8)
     # identity-scale crop: side 40 from a 40-pixel rectangle copies the pixels (INTER_LINEAR at integer positions)
-    crop, m = ce.crop_frame(img, (30.0, 20.0, 40.0, 40.0), 40, (40, 40), mirror=False)
+    m = ce.crop_matrix((30.0, 20.0, 40.0, 40.0), 40, mirror=False)
+    crop = port.crop_warp(img, m, (40, 40))
     assert m.tolist() == [[1.0, 0.0, 30.0], [0.0, 1.0, 20.0]]
     want = img[20:60, 30:70].transpose(2, 0, 1).astype(np.float32) / 256.0 - 0.5
     assert np.array_equal(crop, want.astype(np.float32))
     # mirrored (left hand): column u of the crop is image column x + width - u
-    crop_m, mm = ce.crop_frame(img, (30.0, 20.0, 40.0, 40.0), 40, (40, 40), mirror=True)
+    mm = ce.crop_matrix((30.0, 20.0, 40.0, 40.0), 40, mirror=True)
+    crop_m = port.crop_warp(img, mm, (40, 40))
     assert mm.tolist() == [[-1.0, 0.0, 70.0], [0.0, 1.0, 20.0]]
     assert np.array_equal(crop_m[:, :, 1:], want[:, :, ::-1][:, :, :-1].astype(np.float32))
     # back-projection: double-precision affine, float result
@@ -113,7 +114,7 @@ def test_crop_math():
     out = ce.connect_keypoints(peaks, mm)
     assert np.array_equal(out, np.array([[60.0, 25.0, 0.7], [69.5, 59.25, 0.1]], np.float32))
     # scaled crop: rectangle 80 -> side 40, scale 2
-    _, m2 = ce.crop_frame(img, (10.0, 10.0, 80.0, 80.0), 40, (40, 40), mirror=False)
+    m2 = ce.crop_matrix((10.0, 10.0, 80.0, 80.0), 40, mirror=False)
     assert m2[0, 0] == 2.0 and m2[1, 1] == 2.0 and m2[0, 2] == 10.0
     assert ce.recenter((10.0, 20.0, 40.0, 40.0), 60.0, 60.0) == (0.0, 10.0, 60.0, 60.0)
     kp = np.array([[0, 0, 0.25], [0, 0, 0.5], [0, 0, 0.75]], np.float32)

@@ -117,11 +117,11 @@ def test_hand_extractor_batched_equals_serial_and_oracle(port, cuda):
         assert np.array_equal(hx.getHandKeypoints()[hand][0], kps[hand][person])
         assert np.array_equal(hx.getHeatMaps()[hand][0], heat[hand][person])
     # one crop against the FP32 oracle: heat-maps within tolerance, key-points = back-projected arg-max
-    crop, aff = ce.crop_frame(img, rects[0][1], 368, (368, 368), mirror=False)
+    crop = port.crop_warp(img, ce.crop_matrix(rects[0][1], 368, mirror=False), (368, 368))
     want = port.resize_merge([ref.forward(crop[None])["net_output"][0]], 368, 368)
     assert np.abs(np.clip(want[:21], 0, 1) - heat[1][0]).max() <= TOL_NET
     raw = hx._net.heat                                                    # last run: the (1, person 1) crop
-    crop1, aff1 = ce.crop_frame(img, rects[1][1], 368, (368, 368), mirror=False)
+    aff1 = ce.crop_matrix(rects[1][1], 368, mirror=False)
     peaks = port.maximum(raw[0].cpu().numpy(), 21)
     assert np.array_equal(ce.connect_keypoints(peaks, aff1), kps[1][1])
 
@@ -163,9 +163,7 @@ def test_face_extractor(port, cuda):
         m = np.array([[r[2] / 368.0, 0.0, r[0]], [0.0, r[2] / 368.0, r[1]]])
         assert np.array_equal(kp[person], ce.connect_keypoints(port.maximum(raw[j], 70), m))
         assert np.array_equal(heat[person], np.clip(raw[j][:70], 0, 1) * np.float32(2.0) - np.float32(1.0))
-    import cv2
     m0 = np.array([[128.0 / 368.0, 0.0, 40.0], [0.0, 128.0 / 368.0, 30.0]])
-    crop = ce.u_char_to_float(cv2.warpAffine(img, m0, (368, 368), flags=cv2.INTER_LINEAR | cv2.WARP_INVERSE_MAP,
-                                             borderMode=cv2.BORDER_CONSTANT, borderValue=(0, 0, 0)))
+    crop = port.crop_warp(img, m0, (368, 368))
     want = port.resize_merge([ref.forward(crop[None])["net_output"][0]], 368, 368)
     assert np.abs(want - raw[0]).max() <= TOL_NET
