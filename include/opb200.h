@@ -104,6 +104,24 @@ opb200_status opb200_crop_warp(float* dst, const unsigned char* frame, const dou
                                int src_h, int src_w, int dst_h, int dst_w, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
+ * Heat-map export -- replaces the per-group cudaMemcpy + host remap loops of op::PoseExtractorNet::getHeatMapsCopy
+ * (reference: src/openpose/pose/poseExtractorNet.cpp:106-243; the hand / face extractors apply the body-part rules,
+ * handExtractorCaffe.cpp / faceExtractorCaffe.cpp updateHeatMapsForPerson). heat (N,C,H,W): channels
+ * [0,parts) body parts, then 1 background channel when has_bkg, then paf_channels PAF channels. types_mask selects
+ * the groups (OPB200_HEATMAP_*, bit = 1 << op::HeatMapType); scale_mode is the op::ScaleMode value (3..8:
+ * ZeroToOne, ZeroToOneFixedAspect, PlusMinusOne, PlusMinusOneFixedAspect, UnsignedChar, NoScale; 0..2 clamp only,
+ * the reference's final else branch).
+ * dst (N, opb200_heatmaps_export_channels(...), H, W) fp32: a device buffer, or pinned host memory mapped into the
+ * device address space (cudaHostAlloc / cudaHostRegister), which the kernel writes directly.
+ * ------------------------------------------------------------------------------------------------- */
+#define OPB200_HEATMAP_PARTS 1
+#define OPB200_HEATMAP_BACKGROUND 2
+#define OPB200_HEATMAP_PAFS 4
+int opb200_heatmaps_export_channels(int parts, int has_bkg, int paf_channels, int types_mask);
+opb200_status opb200_heatmaps_export(float* dst, const float* heat, const int heat_shape[4], int parts, int has_bkg,
+                                     int paf_channels, int types_mask, int scale_mode, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
  * bodyPartConnector -- replaces op::connectBodyPartsGpu<float> / op::connectBodyPartsCpu<float>
  * (reference: include/openpose/net/bodyPartConnectorBase.hpp:8-24, src/openpose/net/bodyPartConnectorBase.cpp:
  * 12-75 getScoreAB, 157-472 createPeopleVector, 721-884 filter, 887-934 output; .cu:15-66,108-145 scores).

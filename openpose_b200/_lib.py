@@ -46,6 +46,9 @@ SYMBOLS = {
                                     C.c_float, C.c_void_p]),
     "opb200_crop_warp": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                    C.c_void_p]),
+    "opb200_heatmaps_export_channels": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int]),
+    "opb200_heatmaps_export": (C.c_int, [C.c_void_p, C.c_void_p, _I4, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                         C.c_void_p]),
     "opb200_connect_scratch_bytes": (C.c_size_t, [C.POINTER(ConnectParams), C.c_int]),
     "opb200_connect": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                  C.c_void_p, _I4, C.POINTER(ConnectParams), C.c_void_p]),

@@ -27,7 +27,7 @@ from . import _lib
 from . import net as netmod
 from . import post
 from ._lib import Opb200Error
-from .pose_extractor import HeatMapType, ScaleMode, maximum_top_shape, positive_int_round, remap_heat_maps, \
+from .pose_extractor import HeatMapType, ScaleMode, maximum_top_shape, positive_int_round, \
     resize_and_merge_top_shape
 
 HAND_NUMBER_PARTS = 21           # include/openpose/hand/handParameters.hpp:11
@@ -130,9 +130,11 @@ class _CropNet:
         return self.peaks[:, 0].cpu().numpy()
 
 
-def _heat_maps_for_person(heat_crop: torch.Tensor, parts: int, mode: ScaleMode) -> np.ndarray:
-    """updateHandHeatMapsForPerson / updateFaceHeatMapsForPerson: the part channels, body-part remap rules."""
-    return remap_heat_maps(heat_crop[:parts], None, None, mode)[0].cpu().numpy()
+def _heat_maps_for_crops(heat: torch.Tensor, parts: int, mode: ScaleMode) -> np.ndarray:
+    """updateHandHeatMapsForPerson / updateFaceHeatMapsForPerson for every crop at once: the part channels under the
+    body-part remap rules, written by one kernel straight into pinned host memory -> (N, parts, H, W)."""
+    with torch.cuda.device(heat.device):
+        return post.heatmaps_export_gpu(heat, parts, True, 0, post.HEATMAP_PARTS, mode).numpy()
 
 
 class HandExtractorB200:
@@ -207,9 +209,9 @@ class HandExtractorB200:
                 self.mHandKeypoints[hand][person] = est
             best[(hand, person)] = j        # the reference stores the heat-maps of the LAST scale processed
         if want_heat:
+            exported = _heat_maps_for_crops(self._net.heat, HAND_NUMBER_PARTS, self.mHeatMapScaleMode)
             for (hand, person), j in best.items():
-                self.mHeatMaps[hand][person] = _heat_maps_for_person(self._net.heat[j], HAND_NUMBER_PARTS,
-                                                                     self.mHeatMapScaleMode)
+                self.mHeatMaps[hand][person] = exported[j]
 
 
 class FaceExtractorB200:
@@ -264,8 +266,8 @@ class FaceExtractorB200:
             return
         frame = upload_frame(cvInputData, torch.device("cuda", self._net.gpu))
         peaks = self._net.run(crop_frames_gpu(frame, [j[1] for j in jobs], self.mNetOutputSize))
+        exported = _heat_maps_for_crops(self._net.heat, FACE_NUMBER_PARTS, self.mHeatMapScaleMode) if want_heat else None
         for j, (person, m) in enumerate(jobs):
             self.mFaceKeypoints[person] = connect_keypoints(peaks[j], m)
             if want_heat:
-                self.mHeatMaps[person] = _heat_maps_for_person(self._net.heat[j], FACE_NUMBER_PARTS,
-                                                               self.mHeatMapScaleMode)
+                self.mHeatMaps[person] = exported[j]

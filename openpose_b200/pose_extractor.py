@@ -100,39 +100,6 @@ def maximum_top_shape(bottom_shape: Sequence[int]) -> List[int]:
     return [bottom_shape[0], 1, bottom_shape[1] - 1, 3]
 
 
-def _fast_truncate(t: torch.Tensor, lo: float = 0.0, hi: float = 1.0) -> torch.Tensor:
-    return torch.clamp(t, lo, hi)
-
-
-def remap_heat_maps(parts: Optional[torch.Tensor], bkg: Optional[torch.Tensor], pafs: Optional[torch.Tensor],
-                    mode: ScaleMode) -> List[torch.Tensor]:
-    """Range remap of getHeatMapsCopy (poseExtractorNet.cpp:139-227), separate multiply and add as in the C++."""
-    out = []
-    pm = mode in (ScaleMode.PlusMinusOne, ScaleMode.PlusMinusOneFixedAspect)
-    zo = mode in (ScaleMode.ZeroToOne, ScaleMode.ZeroToOneFixedAspect)
-    for t in (parts, bkg):
-        if t is None:
-            continue
-        if mode == ScaleMode.NoScale:
-            out.append(t)
-        elif pm:
-            out.append(_fast_truncate(t) * 2.0 - 1.0)
-        elif mode == ScaleMode.UnsignedChar:
-            out.append(torch.trunc(_fast_truncate(t) * 255.0 + 0.5))
-        else:
-            out.append(_fast_truncate(t))
-    if pafs is not None:
-        if mode == ScaleMode.NoScale:
-            out.append(pafs)
-        elif zo:
-            out.append(_fast_truncate(pafs, -1.0) * 0.5 + 0.5)
-        elif mode == ScaleMode.UnsignedChar:
-            out.append(torch.trunc((_fast_truncate(pafs, -1.0) * 128.5 + 128.5) + 0.5))
-        else:
-            out.append(_fast_truncate(pafs, -1.0))
-    return out
-
-
 class PoseExtractorB200:
     """Body-pose extractor on one GPU. One instance per GPU, initialised and used on one thread, as the reference's."""
 
@@ -283,12 +250,10 @@ class PoseExtractorB200:
             return np.zeros((0,), np.float32)
         parts = pose_number_body_parts(self.mPoseModel)
         pairs = post.model_dims(self.mPoseModel)[1]
-        hm = self.spHeatMapsBlob[0]
-        p = hm[:parts] if HeatMapType.Parts in self.mHeatMapTypes else None
-        b = hm[parts:parts + 1] if HeatMapType.Background in self.mHeatMapTypes else None
-        f = hm[parts + 1:parts + 1 + 2 * pairs] if HeatMapType.PAFs in self.mHeatMapTypes else None
-        groups = remap_heat_maps(p, b, f, self.mHeatMapScaleMode)
-        return torch.cat(groups, dim=0).cpu().numpy()
+        mask = sum(1 << int(t) for t in set(self.mHeatMapTypes))
+        hm = self.spHeatMapsBlob[0:1]
+        with torch.cuda.device(hm.device):
+            return post.heatmaps_export_gpu(hm, parts, True, 2 * pairs, mask, self.mHeatMapScaleMode)[0].numpy()
 
     def getCandidatesCopy(self) -> List[List[Tuple[float, float, float]]]:
         """Per body part: [(x * scaleNetToOutput, y * scaleNetToOutput, score)] of the first count peaks."""

@@ -81,6 +81,28 @@ def maximum_gpu(target: torch.Tensor, source: torch.Tensor) -> torch.Tensor:
     return target
 
 
+HEATMAP_PARTS, HEATMAP_BACKGROUND, HEATMAP_PAFS = 1, 2, 4      # 1 << op::HeatMapType
+
+
+def heatmaps_export_gpu(heat: torch.Tensor, parts: int, has_bkg: bool, paf_channels: int, types_mask: int,
+                        scale_mode: int, to_host: bool = True) -> torch.Tensor:
+    """getHeatMapsCopy's group selection + range remap (poseExtractorNet.cpp:106-243) for a batch (N,C,H,W) in one
+    launch. to_host: the kernel writes straight into pinned host memory (returned tensor, valid after the sync done
+    here); otherwise a device tensor."""
+    L = _lib.lib()
+    n, _, h, w = heat.shape
+    ch = L.opb200_heatmaps_export_channels(parts, int(has_bkg), paf_channels, types_mask)
+    if to_host:
+        dst = torch.empty((n, ch, h, w), dtype=torch.float32, pin_memory=True)
+    else:
+        dst = torch.empty((n, ch, h, w), dtype=torch.float32, device=heat.device)
+    _lib.check(L.opb200_heatmaps_export(dst.data_ptr(), _dev(heat, "heat"), _lib.i4(heat.shape), parts, int(has_bkg),
+                                        paf_channels, types_mask, int(scale_mode), _stream_ptr()))
+    if to_host:
+        torch.cuda.current_stream().synchronize()
+    return dst
+
+
 def pose_defaults(pose_model: int, maximize_positives: bool = False) -> dict:
     """Default thresholds, reference: src/openpose/pose/poseParameters.cpp:677-756 (BODY_25 / COCO_18)."""
     mp = maximize_positives

@@ -75,6 +75,8 @@ class Port:
         L.opo_preprocess.argtypes = [_f32p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float]
         L.opo_crop_warp.restype = None
         L.opo_crop_warp.argtypes = [_f32p, C.c_void_p, C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int, C.c_int]
+        L.opo_heatmaps_export.restype = C.c_int
+        L.opo_heatmaps_export.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
         L.opo_pair_scores.restype = None
         L.opo_pair_scores.argtypes = [_f32p, _f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
                                       C.c_float, C.c_float, C.c_int]
@@ -137,6 +139,18 @@ class Port:
         out = np.empty((3, int(size[1]), int(size[0])), np.float32)
         self.lib.opo_crop_warp(_fp(out), frame.ctypes.data_as(C.c_void_p), m.ctypes.data_as(C.POINTER(C.c_double)),
                                frame.shape[0], frame.shape[1], out.shape[1], out.shape[2])
+        return out
+
+    def heatmaps_export(self, heat: np.ndarray, parts: int, has_bkg: bool, pafs: int, mask: int, mode: int):
+        """heat (C,H,W) of one frame -> (selected,H,W); None when the background is requested but absent."""
+        heat = np.ascontiguousarray(heat, np.float32)
+        _, h, w = heat.shape
+        n = (parts if mask & 1 else 0) + (1 if (mask & 2) and has_bkg else 0) + (pafs if mask & 4 else 0)
+        out = np.empty((n, h, w), np.float32)
+        rc = self.lib.opo_heatmaps_export(_fp(out), _fp(heat), h * w, parts, int(has_bkg), pafs, mask, mode)
+        if rc < 0:
+            return None
+        assert rc == n
         return out
 
     def pair_scores(self, heat, peaks, model, p=None, max_peaks=MAX_PEAKS, mode=MODE_CPU) -> np.ndarray:

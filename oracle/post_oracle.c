@@ -265,6 +265,68 @@ void opo_crop_warp(float* dst, const unsigned char* frame, const double* m, int 
 }
 
 /* ------------------------------------------------------------------------------------------------
+ * getHeatMapsCopy: src/openpose/pose/poseExtractorNet.cpp:106-243 -- group by group: copy, then the scalar remap
+ * loop for the ScaleMode (fastTruncate = compare-and-select of include/openpose/utilities/fastMath.hpp:72-88,
+ * positiveIntRound = (int)(a + 0.5f)). heat: (channels, hw) of one frame = parts | background (has_bkg) | pafs.
+ * mask bits: 1 parts, 2 background, 4 PAFs; mode = op::ScaleMode value. Returns the number of channels written,
+ * -1 when the background is requested for a model without one (:196-200).
+ * ------------------------------------------------------------------------------------------------ */
+static float fast_max(float a, float b) { return a > b ? a : b; }
+static float fast_min(float a, float b) { return a < b ? a : b; }
+static float fast_truncate(float v, float lo, float hi) { return fast_min(hi, fast_max(lo, v)); }
+
+int opo_heatmaps_export(float* dst, const float* heat, int hw, int parts, int has_bkg, int pafs, int mask, int mode)
+{
+    enum { ZeroToOne = 3, ZeroToOneFixedAspect, PlusMinusOne, PlusMinusOneFixedAspect, UnsignedChar, NoScale };
+    size_t off = 0;
+    int written = 0;
+    for (int group = 0; group < 2; group++) /* body parts, then background: same rules (:130-194) */
+    {
+        if (!(mask & (1 << group)))
+            continue;
+        if (group == 1 && !has_bkg)
+            return -1;
+        const size_t vol = (size_t)(group == 0 ? parts : 1) * hw;
+        float* d = dst + off;
+        memcpy(d, heat + (group == 0 ? 0 : (size_t)parts * hw), vol * sizeof(float));
+        if (mode != NoScale)
+        {
+            if (mode == PlusMinusOne || mode == PlusMinusOneFixedAspect)
+                for (size_t i = 0; i < vol; i++)
+                    d[i] = fast_truncate(d[i], 0.f, 1.f) * 2.f - 1.f;
+            else if (mode == UnsignedChar)
+                for (size_t i = 0; i < vol; i++)
+                    d[i] = (float)pos_int_round(fast_truncate(d[i], 0.f, 1.f) * 255.f);
+            else
+                for (size_t i = 0; i < vol; i++)
+                    d[i] = fast_truncate(d[i], 0.f, 1.f);
+        }
+        off += vol;
+        written += group == 0 ? parts : 1;
+    }
+    if (mask & 4) /* PAFs (:203-229) */
+    {
+        const size_t vol = (size_t)pafs * hw;
+        float* d = dst + off;
+        memcpy(d, heat + (size_t)(parts + (has_bkg ? 1 : 0)) * hw, vol * sizeof(float));
+        if (mode != NoScale)
+        {
+            if (mode == ZeroToOne || mode == ZeroToOneFixedAspect)
+                for (size_t i = 0; i < vol; i++)
+                    d[i] = fast_truncate(d[i], -1.f, 1.f) * 0.5f + 0.5f;
+            else if (mode == UnsignedChar)
+                for (size_t i = 0; i < vol; i++)
+                    d[i] = (float)pos_int_round(fast_truncate(d[i], -1.f, 1.f) * 128.5f + 128.5f);
+            else
+                for (size_t i = 0; i < vol; i++)
+                    d[i] = fast_truncate(d[i], -1.f, 1.f);
+        }
+        written += pafs;
+    }
+    return written;
+}
+
+/* ------------------------------------------------------------------------------------------------
  * maximum: src/openpose/net/maximumBase.cpp:8-57 (cv::minMaxLoc = first maximum in raster order),
  * src/openpose/net/maximumBase.cu:85-113. target (parts, 3) = (x, y, value); background (last) skipped.
  * ------------------------------------------------------------------------------------------------ */

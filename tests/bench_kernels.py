@@ -37,6 +37,16 @@ def main():
         ms = timeit(lambda: preprocess_gpu(dst, frames, scale))
         gb = n * (hs * ws * 3 + 3 * 368 * 656 * 4) / 1e9
         print("preprocess %dx%d x%d: %.3f ms  %.0f GB/s" % (ws, hs, n, ms, gb / ms * 1e3))
+    heat = torch.rand((16, 78, 368, 656), device=dev)
+    for mode, name in ((8, "NoScale"), (7, "UnsignedChar"), (3, "ZeroToOne")):
+        ms = timeit(lambda: post.heatmaps_export_gpu(heat, 25, True, 52, 7, mode, to_host=False))
+        gb = 2 * heat.numel() * 4 / 1e9
+        print("heatmaps_export %s x16 -> device: %.3f ms  %.0f GB/s" % (name, ms, gb / ms * 1e3))
+    one = heat[:1]
+    ms = timeit(lambda: post.heatmaps_export_gpu(one, 25, True, 52, 7, 3, to_host=True), reps=10)
+    print("heatmaps_export 1 frame -> pinned host: %.3f ms  %.1f GB/s over the link" % (ms, one.numel() * 4 / 1e6 / ms))
+    ms = timeit(lambda: one.clamp(0, 1).cpu(), reps=10)
+    print("torch clamp + .cpu() 1 frame (pageable): %.3f ms" % ms)
 
 
 if __name__ == "__main__":

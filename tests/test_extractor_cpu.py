@@ -37,13 +37,17 @@ def test_scale_net_to_output_config1():
 
 
 @pytest.mark.parametrize("mode", list(pe.ScaleMode))
-def test_remap_heat_maps_matches_scalar_rules(mode):
-    """poseExtractorNet.cpp:139-227 restated element by element in float32."""
+def test_heatmaps_export_oracle_matches_scalar_rules(port, mode):
+    """poseExtractorNet.cpp:139-227 restated element by element in float32 numpy vs the C oracle."""
     rng = np.random.default_rng(int(mode))
     parts = rng.uniform(-0.3, 1.3, (3, 5, 7)).astype(np.float32)
     bkg = rng.uniform(-0.3, 1.3, (1, 5, 7)).astype(np.float32)
     pafs = rng.uniform(-1.4, 1.4, (4, 5, 7)).astype(np.float32)
-    got = pe.remap_heat_maps(torch.from_numpy(parts), torch.from_numpy(bkg), torch.from_numpy(pafs), mode)
+    heat = np.concatenate([parts, bkg, pafs])
+    got_all = port.heatmaps_export(heat, 3, True, 4, 7, int(mode))
+    got = [torch.from_numpy(got_all[:3]), torch.from_numpy(got_all[3:4]), torch.from_numpy(got_all[4:])]
+    assert np.array_equal(port.heatmaps_export(heat, 3, True, 4, 4 | 1, int(mode)), np.concatenate([got_all[:3], got_all[4:]]))
+    assert port.heatmaps_export(np.concatenate([parts, pafs]), 3, False, 4, 2, int(mode)) is None   # no bkg channel
     f = np.float32
     trunc = lambda v, lo=0.0: np.minimum(np.maximum(v, f(lo)), f(1.0))   # noqa: E731
     def body(v):
