@@ -156,6 +156,36 @@ opb200_status opb200_paf_scores(float* cube, const float* heat, const float* pea
                                 const opb200_connect_params* p, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
+ * People post-steps on the connector's output layout (keypoints (N,capacity,parts,3), scores (N,capacity),
+ * count (N) int32, all on the device), so body -> rectangles -> crops -> hand / face stays on the device.
+ *
+ * opb200_keep_top_people -- replaces op::KeepTopNPeople::keepTopPeople
+ *   (reference: include/openpose/core/keepTopNPeople.hpp, src/openpose/core/keepTopNPeople.cpp:17-91):
+ *   score * sqrt(area of the box around parts with score > 0.05), the number_people_max best kept in their
+ *   original order, ties on the threshold filled in order; frames with <= number_people_max people (or
+ *   number_people_max <= 0) are copied unchanged. out_* have the input layout; out_scores carries the kept
+ *   people's scores (the reference leaves the score array untouched).
+ * opb200_keypoint_scale_and_offset / opb200_scale_keypoints -- replace op::KeypointScaler::scale
+ *   (reference: src/openpose/core/keypointScaler.cpp:7-104; op::scaleKeypoints2d,
+ *   src/openpose/utilities/keypoint.cpp:104-168): host helper -> {offset x, offset y, scale x, scale y} for an
+ *   op::ScaleMode, then x*sx[+ox], y*sy[+oy] in place (count may be NULL = all `capacity` rows, e.g. for hand /
+ *   face keypoint arrays).
+ * opb200_hand_face_rectangles -- replaces op::HandDetector::detectHands and op::FaceDetector::detectFaces
+ *   (reference: src/openpose/hand/handDetector.cpp:9-46,136-164, src/openpose/face/faceDetector.cpp:22-141):
+ *   hand_rectangles (N,capacity,2,4) = left, right (x, y, w, h); face_rectangles (N,capacity,4); either may be NULL.
+ * ------------------------------------------------------------------------------------------------- */
+opb200_status opb200_keep_top_people(float* out_keypoints, float* out_scores, int* out_count,
+                                     const float* keypoints, const float* scores, const int* count, int n_frames,
+                                     int capacity, int parts, int number_people_max, void* stream);
+opb200_status opb200_keypoint_scale_and_offset(float out[4], int scale_mode, double scale_input_to_output,
+                                               double scale_net_to_output, int producer_w, int producer_h);
+opb200_status opb200_scale_keypoints(float* keypoints, const int* count, int n_frames, int capacity, int parts,
+                                     float scale_x, float scale_y, float offset_x, float offset_y, void* stream);
+opb200_status opb200_hand_face_rectangles(float* hand_rectangles, float* face_rectangles, const float* keypoints,
+                                          const int* count, int n_frames, int capacity, int pose_model,
+                                          void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
  * NetB200 -- replaces op::NetCaffe behind op::Net
  * (reference: include/openpose/net/net.hpp:8-18, include/openpose/net/netCaffe.hpp:12-13,
  *  src/openpose/net/netCaffe.cpp:45-99 constructor checks, :154-210 initializationOnThread,

@@ -49,6 +49,14 @@ SYMBOLS = {
     "opb200_heatmaps_export_channels": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int]),
     "opb200_heatmaps_export": (C.c_int, [C.c_void_p, C.c_void_p, _I4, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                          C.c_void_p]),
+    "opb200_keep_top_people": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "opb200_keypoint_scale_and_offset": (C.c_int, [C.POINTER(C.c_float), C.c_int, C.c_double, C.c_double, C.c_int,
+                                                   C.c_int]),
+    "opb200_scale_keypoints": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
+                                         C.c_float, C.c_float, C.c_void_p]),
+    "opb200_hand_face_rectangles": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                              C.c_int, C.c_void_p]),
     "opb200_connect_scratch_bytes": (C.c_size_t, [C.POINTER(ConnectParams), C.c_int]),
     "opb200_connect": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                  C.c_void_p, _I4, C.POINTER(ConnectParams), C.c_void_p]),

@@ -232,6 +232,14 @@ class Ref:
         L.ref_connect_from_pair_scores.restype = C.c_int
         L.ref_connect_from_pair_scores.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_float,
                                                    C.c_float, C.c_int, _f32p, _f32p, C.c_int]
+        L.ref_detect_hands.restype = C.c_int
+        L.ref_detect_hands.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, _f32p]
+        L.ref_detect_faces.restype = C.c_int
+        L.ref_detect_faces.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, _f32p]
+        L.ref_keep_top_people.restype = C.c_int
+        L.ref_keep_top_people.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int, _f32p]
+        L.ref_scale_keypoints.restype = C.c_int
+        L.ref_scale_keypoints.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, C.c_int]
         L.ref_pose_part_pairs.argtypes = [C.c_int, C.POINTER(C.c_uint), C.c_int]
         L.ref_pose_map_index.argtypes = [C.c_int, C.POINTER(C.c_uint), C.c_int]
         L.ref_pose_defaults.argtypes = [C.c_int, C.c_int, _f32p]
@@ -240,6 +248,37 @@ class Ref:
     @staticmethod
     def available() -> bool:
         return os.path.exists(REF_SO) or os.path.exists("/root/reference/src/openpose/net/nmsBase.cpp")
+
+    def _check(self, rc):
+        if rc < 0:
+            raise ValueError(self.lib.ref_last_error().decode())
+        return rc
+
+    def detect_hands(self, kp: np.ndarray, model: int) -> np.ndarray:
+        """HandDetector::detectHands: kp (people, parts, 3) -> (people, 2, 4)."""
+        kp = np.ascontiguousarray(kp, np.float32)
+        out = np.zeros((kp.shape[0], 2, 4), np.float32)
+        self._check(self.lib.ref_detect_hands(_fp(kp), kp.shape[0], kp.shape[1], model, _fp(out)))
+        return out
+
+    def detect_faces(self, kp: np.ndarray, model: int) -> np.ndarray:
+        kp = np.ascontiguousarray(kp, np.float32)
+        out = np.zeros((kp.shape[0], 4), np.float32)
+        self._check(self.lib.ref_detect_faces(_fp(kp), kp.shape[0], kp.shape[1], model, _fp(out)))
+        return out
+
+    def keep_top_people(self, kp: np.ndarray, scores: np.ndarray, n_max: int) -> np.ndarray:
+        kp = np.ascontiguousarray(kp, np.float32)
+        scores = np.ascontiguousarray(scores, np.float32)
+        out = np.zeros_like(kp)
+        n = self._check(self.lib.ref_keep_top_people(_fp(kp), _fp(scores), kp.shape[0], kp.shape[1], n_max, _fp(out)))
+        return out[:n]
+
+    def scale_keypoints(self, kp: np.ndarray, mode: int, scale_in_out: float, scale_net_out: float, producer) -> np.ndarray:
+        kp = np.array(kp, np.float32, order="C")
+        self._check(self.lib.ref_scale_keypoints(_fp(kp), kp.shape[0], kp.shape[1], mode, scale_in_out, scale_net_out,
+                                                 int(producer[0]), int(producer[1])))
+        return kp
 
     def nms(self, heat, thr, channels, off=(0.5, 0.5), max_peaks=MAX_PEAKS, peaks=None) -> np.ndarray:
         heat = np.ascontiguousarray(heat, np.float32)

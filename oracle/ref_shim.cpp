@@ -11,7 +11,11 @@
 //   (2) op::Matrix's default constructor (src/openpose/core/matrix.cpp, needs OpenCV),
 //   (3) op::getKeypointsRoi(Rectangle,Rectangle) (src/openpose/utilities/keypoint.cpp:587-640;
 //       only reachable for >=135-part models, which are out of scope -> aborts),
-//   (4) a plain C entry surface (ref_*) so Python (ctypes) can drive the reference functions.
+//   (4) a plain C entry surface (ref_*) so Python (ctypes) can drive the reference functions,
+//   (5) for the people post-steps (hand/handDetector.cpp, face/faceDetector.cpp, core/keepTopNPeople.cpp,
+//       core/keypointScaler.cpp, utilities/keypoint.cpp -- all compiled unmodified; keypoint.cpp's renderer sees a
+//       type-only opencv2/imgproc stand-in written by oracle/Makefile and is never called): the Array<T> copy / move /
+//       slice constructors, clone, getVolume(a, b) of array.cpp:165-280,470-500 (storage plumbing only).
 // Nothing here restates reference arithmetic: nms / PAF scoring / assembly all run in the
 // reference's own object code.
 #include <cstdio>
@@ -23,6 +27,10 @@
 #include <openpose/core/matrix.hpp>
 #include <openpose/core/point.hpp>
 #include <openpose/core/rectangle.hpp>
+#include <openpose/core/keepTopNPeople.hpp>
+#include <openpose/core/keypointScaler.hpp>
+#include <openpose/face/faceDetector.hpp>
+#include <openpose/hand/handDetector.hpp>
 #include <openpose/net/bodyPartConnectorBase.hpp>
 #include <openpose/net/nmsBase.hpp>
 #include <openpose/pose/poseParameters.hpp>
@@ -94,7 +102,77 @@ namespace op
         return pData[index];
     }
 
+    // (5) storage plumbing
+    template<typename T>
+    Array<T>::Array(const Array<T>& array) :
+        mSize{array.mSize}, mVolume{array.mVolume}, spData{array.spData}, pData{array.pData}
+    {
+    }
+
+    template<typename T>
+    Array<T>::Array(Array<T>&& array) :
+        mSize{array.mSize}, mVolume{array.mVolume}
+    {
+        std::swap(spData, array.spData);
+        std::swap(pData, array.pData);
+    }
+
+    template<typename T>
+    Array<T>::Array(const Array<T>& array, const int index, const bool noCopy)
+    {
+        if (array.getSize(0) <= index)
+        {
+            std::fprintf(stderr, "oracle shim: Array slice index out of range\n");
+            std::abort();
+        }
+        auto sizes = array.getSize();
+        sizes[0] = 1;
+        reset(sizes);      // always the copying flavour: the alias flavour only saves the copy
+        const auto area = mVolume;
+        std::copy(array.pData + index * area, array.pData + (index + 1) * area, pData);
+    }
+
+    template<typename T>
+    Array<T> Array<T>::clone() const
+    {
+        Array<T> array{mSize};
+        std::copy(pData, pData + mVolume, array.pData);
+        return array;
+    }
+
+    template<typename T>
+    size_t Array<T>::getVolume(const int indexA, const int indexB) const
+    {
+        const auto indexBFinal = (indexB != -1 ? indexB : (int)mSize.size() - 1);
+        if (indexA < 0 || indexA > indexBFinal || (size_t)indexBFinal >= mSize.size())
+        {
+            std::fprintf(stderr, "oracle shim: Array::getVolume indexes out of dimension\n");
+            std::abort();
+        }
+        size_t v = 1;
+        for (int i = indexA; i <= indexBFinal; i++)
+            v *= (size_t)mSize[i];
+        return v;
+    }
+
+    template<typename T>
+    Matrix& Array<T>::getCvMat()
+    {
+        std::fprintf(stderr, "oracle shim: Array::getCvMat reached (rendering) - out of scope\n");
+        std::abort();
+    }
+
+    void* Matrix::getCvMat()
+    {
+        std::fprintf(stderr, "oracle shim: Matrix::getCvMat reached (rendering) - out of scope\n");
+        std::abort();
+    }
+
 #define OPREF_INSTANTIATE_ARRAY(T) \
+    template Array<T>::Array(const Array<T>&, const int, const bool); \
+    template Array<T> Array<T>::clone() const; \
+    template size_t Array<T>::getVolume(const int, const int) const; \
+    template Matrix& Array<T>::getCvMat(); \
     template Array<T>::Array(const std::vector<int>&); \
     template void Array<T>::reset(const int); \
     template void Array<T>::reset(const std::vector<int>&); \
@@ -103,6 +181,18 @@ namespace op
     template T& Array<T>::commonAt(const int) const
     OPREF_INSTANTIATE_ARRAY(float);
     OPREF_INSTANTIATE_ARRAY(double);
+
+    // The copy / move constructors cannot be named in an explicit instantiation (the class also has a converting
+    // constructor template); using them once emits them for the reference's objects to link against.
+    template <typename T>
+    size_t emitCopyAndMove(const Array<T>& a)
+    {
+        Array<T> copy{a};
+        Array<T> moved{std::move(copy)};
+        return moved.getVolume();
+    }
+    template size_t emitCopyAndMove(const Array<float>&);
+    template size_t emitCopyAndMove(const Array<double>&);
 
     // (3)
     template <typename T>
@@ -237,5 +327,106 @@ extern "C"
         out[2] = op::getPoseDefaultConnectInterThreshold(model, mp);
         out[3] = (float)op::getPoseDefaultMinSubsetCnt(mp);
         out[4] = op::getPoseDefaultConnectMinSubsetScore(mp);
+    }
+
+    // ---- people post-steps -------------------------------------------------------------------
+    static op::Array<float> peopleArray(const float* kp, int people, int parts)
+    {
+        op::Array<float> a;
+        if (people > 0)
+        {
+            a.reset({people, parts, 3});
+            std::memcpy(a.getPtr(), kp, sizeof(float) * (size_t)people * parts * 3);
+        }
+        return a;
+    }
+
+    // HandDetector::detectHands, src/openpose/hand/handDetector.cpp:136-164. out: (people, 2, 4) = x, y, w, h.
+    int ref_detect_hands(const float* kp, int people, int parts, int poseModel, float* out)
+    {
+        try
+        {
+            const op::HandDetector detector{(op::PoseModel)poseModel};
+            const auto rects = detector.detectHands(peopleArray(kp, people, parts));
+            for (size_t p = 0; p < rects.size(); p++)
+                for (int h = 0; h < 2; h++)
+                {
+                    const auto& r = rects[p][h];
+                    const float v[4] = {r.x, r.y, r.width, r.height};
+                    std::memcpy(out + (p * 2 + h) * 4, v, sizeof(v));
+                }
+            return (int)rects.size();
+        }
+        catch (const std::exception& e)
+        {
+            std::snprintf(gErr, sizeof(gErr), "%s", e.what());
+            return -1;
+        }
+    }
+
+    // FaceDetector::detectFaces, src/openpose/face/faceDetector.cpp:120-141. out: (people, 4).
+    int ref_detect_faces(const float* kp, int people, int parts, int poseModel, float* out)
+    {
+        try
+        {
+            const op::FaceDetector detector{(op::PoseModel)poseModel};
+            const auto rects = detector.detectFaces(peopleArray(kp, people, parts));
+            for (size_t p = 0; p < rects.size(); p++)
+            {
+                const float v[4] = {rects[p].x, rects[p].y, rects[p].width, rects[p].height};
+                std::memcpy(out + p * 4, v, sizeof(v));
+            }
+            return (int)rects.size();
+        }
+        catch (const std::exception& e)
+        {
+            std::snprintf(gErr, sizeof(gErr), "%s", e.what());
+            return -1;
+        }
+    }
+
+    // KeepTopNPeople::keepTopPeople, src/openpose/core/keepTopNPeople.cpp:17-91. Returns the people kept.
+    int ref_keep_top_people(const float* kp, const float* scores, int people, int parts, int numberPeopleMax,
+                            float* out)
+    {
+        try
+        {
+            op::Array<float> sc;
+            if (people > 0)
+            {
+                sc.reset(people);
+                std::memcpy(sc.getPtr(), scores, sizeof(float) * people);
+            }
+            const op::KeepTopNPeople keeper{numberPeopleMax};
+            const auto top = keeper.keepTopPeople(peopleArray(kp, people, parts), sc);
+            if (!top.empty())
+                std::memcpy(out, top.getConstPtr(), sizeof(float) * top.getVolume());
+            return top.getSize(0);
+        }
+        catch (const std::exception& e)
+        {
+            std::snprintf(gErr, sizeof(gErr), "%s", e.what());
+            return -1;
+        }
+    }
+
+    // KeypointScaler::scale, src/openpose/core/keypointScaler.cpp:77-104 (in place).
+    int ref_scale_keypoints(float* kp, int people, int parts, int scaleMode, double scaleInputToOutput,
+                            double scaleNetToOutput, int producerW, int producerH)
+    {
+        try
+        {
+            auto a = peopleArray(kp, people, parts);
+            const op::KeypointScaler scaler{(op::ScaleMode)scaleMode};
+            scaler.scale(a, scaleInputToOutput, scaleNetToOutput, op::Point<int>{producerW, producerH});
+            if (!a.empty())
+                std::memcpy(kp, a.getConstPtr(), sizeof(float) * a.getVolume());
+            return 0;
+        }
+        catch (const std::exception& e)
+        {
+            std::snprintf(gErr, sizeof(gErr), "%s", e.what());
+            return -1;
+        }
     }
 }
