@@ -79,10 +79,16 @@ namespace opb
         return c;
     }
 
-    template <int BN>
+    // PAIR: two CTAs of a cluster (same TPC) work as one cta_group::2 unit on FOUR M tiles (two each) of the same Cout
+    // tile: every CTA loads only half of each weight stage (BN/2 rows), the leader CTA issues M = 256 MMAs that read
+    // both halves, and each CTA's TMEM receives (and its epilogue drains) its own two tiles. Halves the weight
+    // traffic from L2 per SM, which is what bounds the single-CTA kernel on the large layers.
+    template <int BN, bool PAIR>
     __global__ void __launch_bounds__(kConvThreads, 1) convIgemmKernel(const __grid_constant__ ConvParams p)
     {
         using Cfg = ConvCfg<BN>;
+        constexpr int kBStageBytes = PAIR ? Cfg::kBBytes / 2 : Cfg::kBBytes;   // this CTA's part of a weight stage
+        const uint32_t ctaRank = PAIR ? clusterCtaRank() : 0u;
         extern __shared__ uint8_t smemRaw[];
         uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smemRaw) + 1023) & ~uintptr_t(1023));
         const int aStageBytes = 2 * p.aTileBytes;
@@ -90,7 +96,7 @@ namespace opb
         const uint32_t groupPitch = (uint32_t)p.boxW * 128u;                         // bytes between pixel rows
         uint8_t* sA = smem;                                         // aStages x (tile0 | tile1)
         uint8_t* sB = sA + p.aStages * aStageBytes;                 // bStages x (BN x 128 B)
-        uint8_t* sOut = sB + p.bStages * Cfg::kBBytes;              // staging for the TMA store
+        uint8_t* sOut = sB + p.bStages * kBStageBytes;              // staging for the TMA store
         ConvAux* aux = reinterpret_cast<ConvAux*>(sOut + Cfg::kStagingBytes);
 
         // Programmatic dependent launch: let the next layer's CTAs start their prologue on SMs this grid has
@@ -98,8 +104,11 @@ namespace opb
         asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         const int warp = threadIdx.x >> 5;
         const int lane = threadIdx.x & 31;
-        const int numPairs = (p.numMTiles + 1) >> 1;
-        const int numWork = numPairs * p.nTilesN;
+        // a work item = (group of M tiles, Cout tile); the group is a pair per CTA, i.e. a quad per CTA pair
+        const int numGroups = PAIR ? (p.numMTiles + 3) >> 2 : (p.numMTiles + 1) >> 1;
+        const int numWork = numGroups * p.nTilesN;
+        const int workStart = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+        const int workStride = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
         if (warp == 0 && lane == 0)
         {
@@ -123,14 +132,22 @@ namespace opb
             for (int i = 0; i < 2; ++i)
             {
                 mbarInit(&aux->tmemFull[i], 1);
-                mbarInit(&aux->tmemEmpty[i], 256);
+                mbarInit(&aux->tmemEmpty[i], PAIR ? 512 : 256);   // every epilogue thread (of both CTAs) arrives
             }
             fenceBarrierInit();
         }
         if (warp == 2)
-            tmemAlloc<Cfg::kTmemCols>(&aux->tmemBase);
+        {
+            if (PAIR)
+                tmemAllocPair<Cfg::kTmemCols>(&aux->tmemBase);
+            else
+                tmemAlloc<Cfg::kTmemCols>(&aux->tmemBase);
+        }
         tcFenceBefore();
-        __syncthreads();
+        if (PAIR)
+            clusterSync();      // the peer's barriers must be initialised before anything signals them
+        else
+            __syncthreads();
         tcFenceAfter();
         const uint32_t tmemBase = aux->tmemBase;
         // everything above touched only kernel parameters, smem and TMEM; from here on we read the previous
@@ -145,10 +162,10 @@ namespace opb
             {
                 int as = 0, bs = 0;
                 uint32_t aPhase = 0, bPhase = 0;
-                for (int work = blockIdx.x; work < numWork; work += gridDim.x)
+                for (int work = workStart; work < numWork; work += workStride)
                 {
                     const int nt = work % p.nTilesN;
-                    const int pair = work / p.nTilesN;
+                    const int pair = PAIR ? 2 * (work / p.nTilesN) + (int)ctaRank : work / p.nTilesN;
                     const TileCoord t0 = tileCoord(p, 2 * pair), t1 = tileCoord(p, 2 * pair + 1);
                     int chunk = 0;
                     for (int s = 0; s < p.nSeg; ++s)
@@ -162,11 +179,25 @@ namespace opb
                                     uint8_t* dst = sA + as * aStageBytes;
                                     if (leader)
                                     {
-                                        mbarExpectTx(&aux->aFull[as], 2 * boxBytes);
-                                        tmaLoad4d(dst, &p.aMap[s], &aux->aFull[as], c * kConvBlockK, t0.x0 + kx - p.pad,
-                                                  t0.y0 - p.pad, t0.n);
-                                        tmaLoad4d(dst + p.aTileBytes, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
-                                                  t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
+                                        if (PAIR)
+                                        {
+                                            // both CTAs' boxes are counted on the leader CTA's barrier
+                                            const uint32_t bar = mapaShared(smemAddr(&aux->aFull[as]), 0);
+                                            if (ctaRank == 0)
+                                                mbarExpectTx(&aux->aFull[as], 4 * boxBytes);
+                                            tmaLoad4dPair(dst, &p.aMap[s], bar, c * kConvBlockK, t0.x0 + kx - p.pad,
+                                                          t0.y0 - p.pad, t0.n);
+                                            tmaLoad4dPair(dst + p.aTileBytes, &p.aMap[s], bar, c * kConvBlockK,
+                                                          t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
+                                        }
+                                        else
+                                        {
+                                            mbarExpectTx(&aux->aFull[as], 2 * boxBytes);
+                                            tmaLoad4d(dst, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
+                                                      t0.x0 + kx - p.pad, t0.y0 - p.pad, t0.n);
+                                            tmaLoad4d(dst + p.aTileBytes, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
+                                                      t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
+                                        }
                                     }
                                     __syncwarp();
                                     if (++as == p.aStages)
@@ -176,16 +207,28 @@ namespace opb
                                     }
                                 }
                                 const int kb0 = (chunk * p.k + kx) * p.k;
-                                if (p.bResident && work != (int)blockIdx.x)
+                                if (p.bResident && work != workStart)
                                     continue;          // the whole weight tile already sits in shared memory
                                 for (int ky = 0; ky < p.k; ++ky)
                                 {
                                     mbarWait(&aux->bEmpty[bs], bPhase ^ 1);
                                     if (leader)
                                     {
-                                        mbarExpectTx(&aux->bFull[bs], Cfg::kBBytes);
-                                        tmaLoad2d(sB + bs * Cfg::kBBytes, &p.bMap, &aux->bFull[bs],
-                                                  (kb0 + ky) * kConvBlockK, nt * BN);
+                                        if (PAIR)
+                                        {
+                                            // this CTA's half of the Cout tile (bMap box = BN/2 rows)
+                                            if (ctaRank == 0)
+                                                mbarExpectTx(&aux->bFull[bs], Cfg::kBBytes);
+                                            tmaLoad2dPair(sB + bs * kBStageBytes, &p.bMap,
+                                                          mapaShared(smemAddr(&aux->bFull[bs]), 0),
+                                                          (kb0 + ky) * kConvBlockK, nt * BN + (int)ctaRank * (BN / 2));
+                                        }
+                                        else
+                                        {
+                                            mbarExpectTx(&aux->bFull[bs], Cfg::kBBytes);
+                                            tmaLoad2d(sB + bs * Cfg::kBBytes, &p.bMap, &aux->bFull[bs],
+                                                      (kb0 + ky) * kConvBlockK, nt * BN);
+                                        }
                                     }
                                     __syncwarp();
                                     if (++bs == p.bStages)
@@ -201,16 +244,18 @@ namespace opb
         else if (warp == 1)
         {
             // ===================================== MMA issuer ========================================
+            // (pair mode: the leader CTA's warp issues for both CTAs; the peer's warp has nothing to do)
             const bool leader = electOne();
+            if (!PAIR || ctaRank == 0)
             {
-                constexpr uint32_t idesc = instrDescBf16(kConvBlockM, BN);
+                constexpr uint32_t idesc = instrDescBf16(PAIR ? 2 * kConvBlockM : kConvBlockM, BN);
                 int as = 0, bs = 0, acc = 0;
                 uint32_t aPhase = 0, bPhase = 0, accPhase = 0;
                 const int axPerChunk = p.k / p.kxSpan;
                 const int numAx = p.chunksTotal * axPerChunk;           // A stages consumed per work item
                 const uint64_t bBase = smemDescSw128(smemAddr(sB));
                 const uint64_t kyStep = (uint64_t)(p.boxW * 8);         // one box pixel row down, in 16-byte units
-                for (int work = blockIdx.x; work < numWork; work += gridDim.x)
+                for (int work = workStart; work < numWork; work += workStride)
                 {
                     mbarWait(&aux->tmemEmpty[acc], accPhase ^ 1);
                     tcFenceAfter();
@@ -241,18 +286,31 @@ namespace opb
                             {
                                 mbarWait(&aux->bFull[bs], bPhase);
                                 tcFenceAfter();
-                                const uint64_t bDesc = bBase + (uint64_t)(bs * (Cfg::kBBytes >> 4));
+                                const uint64_t bDesc = bBase + (uint64_t)(bs * (kBStageBytes >> 4));
                                 if (leader)
                                 {
 #pragma unroll
                                     for (int kk = 0; kk < kConvBlockK / 16; ++kk)   // 16 bf16 = 32 bytes per MMA along K
                                         if (kk < steps)
                                         {
-                                            mmaBf16(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
-                                            mmaBf16(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                            if (PAIR)
+                                            {
+                                                mmaBf16Pair(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                                mmaBf16Pair(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                            }
+                                            else
+                                            {
+                                                mmaBf16(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                                mmaBf16(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                            }
                                         }
-                                    if (!p.bResident)
-                                        mmaCommit(&aux->bEmpty[bs]);  // weight slot free once these MMAs retire
+                                    if (!p.bResident)   // weight slot free (in both CTAs) once these MMAs retire
+                                    {
+                                        if (PAIR)
+                                            mmaCommitPair(&aux->bEmpty[bs]);
+                                        else
+                                            mmaCommit(&aux->bEmpty[bs]);
+                                    }
                                 }
                                 __syncwarp();
                                 first = 1;
@@ -266,8 +324,13 @@ namespace opb
                                 aDesc1 += kyStep;
                             }
                         }
-                        if (leader)
-                            mmaCommit(&aux->aEmpty[as]);          // activation slot free
+                        if (leader)                               // activation slot free
+                        {
+                            if (PAIR)
+                                mmaCommitPair(&aux->aEmpty[as]);
+                            else
+                                mmaCommit(&aux->aEmpty[as]);
+                        }
                         __syncwarp();
                         if (++as == p.aStages)
                         {
@@ -275,8 +338,13 @@ namespace opb
                             aPhase ^= 1;
                         }
                     }
-                    if (leader)
-                        mmaCommit(&aux->tmemFull[acc]);           // both accumulators complete -> epilogue
+                    if (leader)                                   // both accumulators complete -> epilogue(s)
+                    {
+                        if (PAIR)
+                            mmaCommitPair(&aux->tmemFull[acc]);
+                        else
+                            mmaCommit(&aux->tmemFull[acc]);
+                    }
                     __syncwarp();
                     if (++acc == 2)
                     {
@@ -303,10 +371,10 @@ namespace opb
             int acc = 0;
             uint32_t accPhase = 0;
             int lastNt = -1;
-            for (int work = blockIdx.x; work < numWork; work += gridDim.x)
+            for (int work = workStart; work < numWork; work += workStride)
             {
                 const int nt = work % p.nTilesN;
-                const int pair = work / p.nTilesN;
+                const int pair = PAIR ? 2 * (work / p.nTilesN) + (int)ctaRank : work / p.nTilesN;
                 if (nt != lastNt)
                 {
                     namedBarrier(1, 256);             // everybody is done with the previous table
@@ -427,7 +495,10 @@ namespace opb
                 }
                 // all TMEM reads of this thread are complete (wait::ld above): hand both accumulators back
                 tcFenceBefore();
-                mbarArrive(&aux->tmemEmpty[acc]);
+                if (PAIR)   // the MMA issuer lives in the leader CTA: both CTAs' epilogues report to its barrier
+                    mbarArriveCluster(mapaShared(smemAddr(&aux->tmemEmpty[acc]), 0));
+                else
+                    mbarArrive(&aux->tmemEmpty[acc]);
                 if (++acc == 2)
                 {
                     acc = 0;
@@ -438,9 +509,18 @@ namespace opb
                 tmaStoreWaitAll();
         }
         tcFenceBefore();
-        __syncthreads();
-        if (warp == 2)
-            tmemFree<Cfg::kTmemCols>(tmemBase);
+        if (PAIR)
+        {
+            clusterSync();      // neither CTA may exit (or free TMEM) while the other can still signal or read it
+            if (warp == 2)
+                tmemFreePair<Cfg::kTmemCols>(tmemBase);
+        }
+        else
+        {
+            __syncthreads();
+            if (warp == 2)
+                tmemFree<Cfg::kTmemCols>(tmemBase);
+        }
     }
 
     // Pipeline depths for a given kernel size: 4 weight stages, as many activation stages as fit (2..4).
@@ -451,18 +531,19 @@ namespace opb
 
     // bStagesAll = weight stages of one whole Cout tile (chunks * k * k); when there is a single Cout tile and they all
     // fit next to two activation stages, the weights are loaded once per CTA and stay resident.
-    template <int BN>
+    template <int BN, bool PAIR>
     static bool convSmemPlan(int k, int kxSpan, int bStagesAll, bool singleNTile, int& aStages, int& bStages,
                              int& resident, int& smemBytes)
     {
         using Cfg = ConvCfg<BN>;
+        constexpr int kBStage = PAIR ? Cfg::kBBytes / 2 : Cfg::kBBytes;   // per CTA
         const int aStage = 2 * convTileBytes(k, kxSpan);
         // weight stages: as many as fit next to two activation stages, up to `want` (one weight stage is only
         // 8 MMAs of tensor time, so the stream needs depth to cover the TMA round trip)
-        int want = (kxSpan > 1 || BN <= 64) ? 6 : 4;
+        int want = (kxSpan > 1 || BN <= 64 || PAIR) ? 6 : 4;
         if (const char* e = std::getenv("OPB200_BSTAGES"))
             want = std::atoi(e);
-        const int fitB = (kSmemLimit - (Cfg::kStagingBytes + kAuxBytes + 1024) - 2 * aStage) / Cfg::kBBytes;
+        const int fitB = (kSmemLimit - (Cfg::kStagingBytes + kAuxBytes + 1024) - 2 * aStage) / kBStage;
         bStages = want < fitB ? want : fitB;
         if (bStages > kMaxBStages)
             bStages = kMaxBStages;
@@ -470,12 +551,12 @@ namespace opb
             return false;
         resident = 0;
         if (singleNTile && bStagesAll <= kMaxBStages &&
-            Cfg::kStagingBytes + kAuxBytes + 1024 + bStagesAll * Cfg::kBBytes + 2 * aStage <= kSmemLimit)
+            Cfg::kStagingBytes + kAuxBytes + 1024 + bStagesAll * kBStage + 2 * aStage <= kSmemLimit)
         {
             bStages = bStagesAll;
             resident = 1;
         }
-        const int fixed = Cfg::kStagingBytes + kAuxBytes + 1024 /*alignment slack*/ + bStages * Cfg::kBBytes;
+        const int fixed = Cfg::kStagingBytes + kAuxBytes + 1024 /*alignment slack*/ + bStages * kBStage;
         aStages = (kSmemLimit - fixed) / aStage;
         if (aStages > kMaxAStages)
             aStages = kMaxAStages;
@@ -483,11 +564,11 @@ namespace opb
         return aStages >= 2;
     }
 
-    template <int BN>
+    template <int BN, bool PAIR>
     static opb200_status launchConvT(ConvParams& p, int gridCap, cudaStream_t st)
     {
         int smemBytes = 0;
-        if (!convSmemPlan<BN>(p.k, p.kxSpan, p.chunksTotal * p.k * p.k, p.nTilesN == 1, p.aStages, p.bStages, p.bResident,
+        if (!convSmemPlan<BN, PAIR>(p.k, p.kxSpan, p.chunksTotal * p.k * p.k, p.nTilesN == 1, p.aStages, p.bStages, p.bResident,
                               smemBytes))
             OPB_FAIL(OPB200_ERR_UNSUPPORTED, "conv: kernel size too large for the shared-memory pipeline");
         p.aTileBytes = convTileBytes(p.k, p.kxSpan);
@@ -496,25 +577,40 @@ namespace opb
         OPB_CUDA(cudaGetDevice(&dev));
         if (!configuredDev[dev & 63])
         {
-            OPB_CUDA(cudaFuncSetAttribute(convIgemmKernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+            OPB_CUDA(cudaFuncSetAttribute(convIgemmKernel<BN, PAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      kSmemLimit));
             configuredDev[dev & 63] = 1;
         }
-        const int numWork = ((p.numMTiles + 1) / 2) * p.nTilesN;
-        int grid = numWork < gridCap ? numWork : gridCap;
-        if (grid < 1)
-            grid = 1;
+        // one CTA per pair of M tiles; in pair mode one 2-CTA cluster per quad
+        const int numWork = (PAIR ? (p.numMTiles + 3) / 4 : (p.numMTiles + 1) / 2) * p.nTilesN;
+        int grid = PAIR ? 2 * (numWork < gridCap / 2 ? numWork : gridCap / 2) : (numWork < gridCap ? numWork : gridCap);
+        if (grid < (PAIR ? 2 : 1))
+            grid = PAIR ? 2 : 1;
         static const bool usePdl = std::getenv("OPB200_NO_PDL") == nullptr;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(grid);
         cfg.blockDim = dim3(kConvThreads);
         cfg.dynamicSmemBytes = smemBytes;
         cfg.stream = st;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cudaLaunchAttribute attr[2];
+        int na = 0;
+        if (PAIR)
+        {
+            attr[na].id = cudaLaunchAttributeClusterDimension;
+            attr[na].val.clusterDim.x = 2;
+            attr[na].val.clusterDim.y = 1;
+            attr[na].val.clusterDim.z = 1;
+            ++na;
+        }
+        if (usePdl)
+        {
+            attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[na].val.programmaticStreamSerializationAllowed = 1;
+            ++na;
+        }
         cfg.attrs = attr;
-        cfg.numAttrs = usePdl ? 1 : 0;
-        OPB_CUDA(cudaLaunchKernelEx(&cfg, convIgemmKernel<BN>, p));
+        cfg.numAttrs = na;
+        OPB_CUDA(cudaLaunchKernelEx(&cfg, convIgemmKernel<BN, PAIR>, p));
         OPB_LAUNCH_CHECK();
         return OPB200_OK;
     }
@@ -525,10 +621,10 @@ namespace opb
             OPB_FAIL(OPB200_ERR_UNSUPPORTED, "conv: kernel size must be odd and at most 7");
         switch (bn)
         {
-        case 32: return launchConvT<32>(p, gridCap, st);
-        case 64: return launchConvT<64>(p, gridCap, st);
-        case 96: return launchConvT<96>(p, gridCap, st);
-        case 128: return launchConvT<128>(p, gridCap, st);
+        case 32: return launchConvT<32, false>(p, gridCap, st);
+        case 64: return p.pairMode ? launchConvT<64, true>(p, gridCap, st) : launchConvT<64, false>(p, gridCap, st);
+        case 96: return p.pairMode ? launchConvT<96, true>(p, gridCap, st) : launchConvT<96, false>(p, gridCap, st);
+        case 128: return p.pairMode ? launchConvT<128, true>(p, gridCap, st) : launchConvT<128, false>(p, gridCap, st);
         default: OPB_FAIL(OPB200_ERR_INVALID, "conv: unsupported BLOCK_N");
         }
     }

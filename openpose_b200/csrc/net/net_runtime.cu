@@ -799,7 +799,14 @@ namespace opb
                 if (st != OPB200_OK)
                     return st;
             }
-            opb200_status st = makeWeightMap(&p.bMap, op.dW, op.kTotal, op.nTilesN * op.bn, op.bn);
+            // CTA-pair kernel (cta_group::2, conv_sm100.cu): halves the weight bytes each SM pulls from L2. Measured
+            // per shape (profiles/r01_net_layer_table_pair_all_b44.txt): +15-25 % on 3x3 layers with >= 2 input chunks and
+            // BN >= 96, slower on 1x1 layers, on the 64-wide trunk layers and on single-chunk layers (short main
+            // loops, where the cross-CTA hand-offs cost more than the traffic saves).
+            // OPB200_CONV_PAIR: 0 = never, 2 = every layer with BN >= 64, unset / 1 = the rule above.
+            static const int pairEnv = std::getenv("OPB200_CONV_PAIR") ? std::atoi(std::getenv("OPB200_CONV_PAIR")) : 1;
+            p.pairMode = (pairEnv == 2 && op.bn >= 64) || (pairEnv == 1 && op.bn >= 96 && op.k >= 3 && op.chunksTotal >= 2);
+            opb200_status st = makeWeightMap(&p.bMap, op.dW, op.kTotal, op.nTilesN * op.bn, p.pairMode ? op.bn / 2 : op.bn);
             if (st != OPB200_OK)
                 return st;
             p.poolFused = op.poolFused ? 1 : 0;

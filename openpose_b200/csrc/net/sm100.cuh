@@ -170,6 +170,81 @@ namespace sm100
         return (1u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((m >> 4) << 24);
     }
 
+    // ---------------------------------------------------------------- CTA pair (cluster of 2, cta_group::2)
+    __device__ __forceinline__ uint32_t clusterCtaRank()
+    {
+        uint32_t r;
+        asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+        return r;
+    }
+    __device__ __forceinline__ void clusterSync()
+    {
+        asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    }
+    // shared::cta address of this CTA -> shared::cluster address of the same offset in CTA `rank` of the cluster
+    __device__ __forceinline__ uint32_t mapaShared(uint32_t addr, uint32_t rank)
+    {
+        uint32_t r;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+        return r;
+    }
+    __device__ __forceinline__ void mbarArriveCluster(uint32_t clusterAddr)
+    {
+        asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(clusterAddr) : "memory");
+    }
+    // TMA loads of a CTA pair: data lands in this CTA's shared memory, the bytes are counted on the mbarrier at
+    // shared::cluster address `barCluster` (the leader CTA's barrier).
+    __device__ __forceinline__ void tmaLoad2dPair(void* dst, const CUtensorMap* m, uint32_t barCluster, int c0, int c1)
+    {
+        asm volatile(
+            "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+            ::"r"(smemAddr(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(barCluster), "r"(c0), "r"(c1)
+            : "memory");
+    }
+    __device__ __forceinline__ void tmaLoad4dPair(void* dst, const CUtensorMap* m, uint32_t barCluster, int c0, int c1,
+                                                  int c2, int c3)
+    {
+        asm volatile(
+            "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+            ::"r"(smemAddr(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(barCluster), "r"(c0), "r"(c1), "r"(c2),
+            "r"(c3)
+            : "memory");
+    }
+    // collective over the pair: the same warp of both CTAs executes it; both get the same column range
+    template <uint32_t kCols>
+    __device__ __forceinline__ void tmemAllocPair(uint32_t* dstSmem)
+    {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smemAddr(dstSmem)),
+                     "n"(kCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    template <uint32_t kCols>
+    __device__ __forceinline__ void tmemFreePair(uint32_t taddr)
+    {
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+    }
+    // M = 256 over the pair: rows 0..127 from this (leader) CTA's A tile, 128..255 from the peer's tile at the same
+    // shared-memory offset; B = N/2 rows from each CTA; each CTA's TMEM receives its own 128 rows. Leader CTA only.
+    __device__ __forceinline__ void mmaBf16Pair(uint32_t tmemD, uint64_t descA, uint64_t descB, uint32_t idesc,
+                                                uint32_t accumulate)
+    {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(tmemD), "l"(descA), "l"(descB), "r"(idesc), "r"(accumulate)
+            : "memory");
+    }
+    // arrive on the barrier at this shared-memory offset in BOTH CTAs once the pair's MMAs have retired
+    __device__ __forceinline__ void mmaCommitPair(uint64_t* bar)
+    {
+        asm volatile(
+            "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+            ::"r"(smemAddr(bar)), "h"((uint16_t)3)
+            : "memory");
+    }
+
     __device__ __forceinline__ void namedBarrier(uint32_t id, uint32_t threads)
     {
         asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
