@@ -30,7 +30,7 @@ namespace opb
     using namespace sm100;
 
     constexpr int kConvThreads = 384;     // 4 role warps + 8 epilogue warps
-    constexpr int kMaxAStages = 4, kMaxBStages = 12;
+    constexpr int kMaxAStages = 4, kMaxBStages = 18;
     constexpr int kSmemLimit = 227 * 1024;
 
     template <int BN>
@@ -50,7 +50,8 @@ namespace opb
         uint64_t tmemFull[2], tmemEmpty[2];
         uint32_t tmemBase;
         uint32_t pad;
-        float2 biasSlope[128];                // (bias, negative-side slope) of the current Cout tile
+        alignas(16) float bias[128];          // bias of the current Cout tile (read as float4)
+        float slope[128];                     // negative-side slope of the current Cout tile
     };
     constexpr int kAuxBytes = 2048;
     static_assert(sizeof(ConvAux) <= kAuxBytes, "aux block too large");
@@ -90,7 +91,7 @@ namespace opb
         constexpr int kBStageBytes = PAIR ? Cfg::kBBytes / 2 : Cfg::kBBytes;   // this CTA's part of a weight stage
         const uint32_t ctaRank = PAIR ? clusterCtaRank() : 0u;
         extern __shared__ uint8_t smemRaw[];
-        uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smemRaw) + 1023) & ~uintptr_t(1023));
+        uint8_t* smem = smemRaw + ((1024u - (smemAddr(smemRaw) & 1023u)) & 1023u);   // 1024-byte aligned
         const int aStageBytes = 2 * p.aTileBytes;
         const uint32_t boxBytes = (uint32_t)p.boxW * (kConvTileH + p.k - 1) * 128u;   // what one TMA box delivers
         const uint32_t groupPitch = (uint32_t)p.boxW * 128u;                         // bytes between pixel rows
@@ -379,7 +380,10 @@ namespace opb
                 {
                     namedBarrier(1, 256);             // everybody is done with the previous table
                     for (int i = et; i < BN; i += 256)
-                        aux->biasSlope[i] = make_float2(__ldg(p.bias + nt * BN + i), __ldg(p.slope + nt * BN + i));
+                    {
+                        aux->bias[i] = __ldg(p.bias + nt * BN + i);
+                        aux->slope[i] = __ldg(p.slope + nt * BN + i);
+                    }
                     lastNt = nt;
                     namedBarrier(1, 256);
                 }
@@ -408,22 +412,39 @@ namespace opb
                     {
                         uint32_t v[32];
                         tmemLoad32(taddr + q * 32, v);
-                        tmemLoadWait();
+                        const uint32_t biasAddr = smemAddr(&aux->bias[q * 32]);
                         float f[32];
+                        float4 b4[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            b4[i] = ldsF4(biasAddr + i * 16);
+                        tmemLoadWait();
                         if (p.actMode == 1)            // ReLU everywhere (the VGG trunk): add + max
                         {
 #pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                f[i] = fmaxf(__uint_as_float(v[i]) + aux->biasSlope[q * 32 + i].x, 0.f);
+                            for (int i = 0; i < 8; ++i)
+                            {
+                                f[4 * i + 0] = fmaxf(__uint_as_float(v[4 * i + 0]) + b4[i].x, 0.f);
+                                f[4 * i + 1] = fmaxf(__uint_as_float(v[4 * i + 1]) + b4[i].y, 0.f);
+                                f[4 * i + 2] = fmaxf(__uint_as_float(v[4 * i + 2]) + b4[i].z, 0.f);
+                                f[4 * i + 3] = fmaxf(__uint_as_float(v[4 * i + 3]) + b4[i].w, 0.f);
+                            }
                         }
                         else
                         {
+                            const uint32_t slopeAddr = smemAddr(&aux->slope[q * 32]);
 #pragma unroll
-                            for (int i = 0; i < 32; ++i)
+                            for (int i = 0; i < 8; ++i)
                             {
-                                const float2 bs = aux->biasSlope[q * 32 + i];
-                                const float a = __uint_as_float(v[i]) + bs.x;
-                                f[i] = a > 0.f ? a : a * bs.y;
+                                const float4 s4 = ldsF4(slopeAddr + i * 16);
+                                const float a0 = __uint_as_float(v[4 * i + 0]) + b4[i].x;
+                                const float a1 = __uint_as_float(v[4 * i + 1]) + b4[i].y;
+                                const float a2 = __uint_as_float(v[4 * i + 2]) + b4[i].z;
+                                const float a3 = __uint_as_float(v[4 * i + 3]) + b4[i].w;
+                                f[4 * i + 0] = a0 > 0.f ? a0 : a0 * s4.x;
+                                f[4 * i + 1] = a1 > 0.f ? a1 : a1 * s4.y;
+                                f[4 * i + 2] = a2 > 0.f ? a2 : a2 * s4.z;
+                                f[4 * i + 3] = a3 > 0.f ? a3 : a3 * s4.w;
                             }
                         }
                         if (p.out32 != nullptr && inImage)
@@ -436,45 +457,55 @@ namespace opb
                                 if (cBase + i < p.cout)
                                     o[i * plane] = f[i];
                         }
-                        if (p.poolFused)
-                        {
-                            // fused 2x2 / stride 2 MAX pooling (Caffe ceil mode: windows are clipped at the image edge):
-                            // the tile origin is even, so a window never straddles tiles, and its four pixels are
-                            // lanes l, l^1 (x) and l^8 (y) of this warp. Pixels outside the image do not take part.
-                            if (!inImage)
-                            {
-#pragma unroll
-                                for (int i = 0; i < 32; ++i)
-                                    f[i] = __int_as_float(0xff800000);
-                            }
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                            {
-                                float m = fmaxf(f[i], __shfl_xor_sync(0xffffffffu, f[i], 1));
-                                f[i] = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
-                            }
-                        }
                         if (p.storeBf16 | p.poolFused)
                         {
-                            // row t of a 128 x 64-byte piece; 16-byte chunk c lands at c ^ ((t >> 1) & 3) (SWIZZLE_64B).
-                            // Pooled: the window anchors (even x, even y) write row (y/2)*4 + x/2 of a 32-row piece.
-                            const int r = p.poolFused ? ((th >> 1) * (kConvTileW / 2) + (tw >> 1)) : t;
-                            uint8_t* row = sOut + q * (kConvBlockM * 64) + r * 64;
-                            const int sw = (r >> 1) & 3;
-                            if (!p.poolFused || ((tw | th) & 1) == 0)
+                            uint32_t pk[16];           // channels (2i, 2i+1) as packed bf16
 #pragma unroll
-                            for (int c = 0; c < 4; ++c)
+                            for (int i = 0; i < 16; ++i)
+                                pk[i] = packBf16(f[2 * i], f[2 * i + 1]);
+                            const uint32_t pieceAddr = smemAddr(sOut + q * (kConvBlockM * 64));
+                            if (p.poolFused)
                             {
-                                uint4 u;
-                                __nv_bfloat162 b0 = __floats2bfloat162_rn(f[c * 8 + 0], f[c * 8 + 1]);
-                                __nv_bfloat162 b1 = __floats2bfloat162_rn(f[c * 8 + 2], f[c * 8 + 3]);
-                                __nv_bfloat162 b2 = __floats2bfloat162_rn(f[c * 8 + 4], f[c * 8 + 5]);
-                                __nv_bfloat162 b3 = __floats2bfloat162_rn(f[c * 8 + 6], f[c * 8 + 7]);
-                                u.x = *reinterpret_cast<uint32_t*>(&b0);
-                                u.y = *reinterpret_cast<uint32_t*>(&b1);
-                                u.z = *reinterpret_cast<uint32_t*>(&b2);
-                                u.w = *reinterpret_cast<uint32_t*>(&b3);
-                                *reinterpret_cast<uint4*>(row + ((c ^ sw) << 4)) = u;
+                                // fused 2x2 / stride 2 MAX pooling (Caffe ceil mode: windows are clipped at the image
+                                // edge): the tile origin is even, so a window never straddles tiles, and its four pixels
+                                // are lanes l, l^1 (x) and l^8 (y) of this warp. Rounding to bf16 is monotonic, so the
+                                // max is taken on the packed values (same bits as max-then-round). The four lanes split
+                                // the 32 channels: each exchange halves what a lane keeps, and every lane ends up with 8
+                                // channels (one 16-byte chunk) of the pooled pixel. Pixels outside the image are -inf.
+                                if (!inImage)
+                                {
+#pragma unroll
+                                    for (int i = 0; i < 16; ++i)
+                                        pk[i] = 0xff80ff80u;
+                                }
+                                const bool xOdd = lane & 1, yOdd = lane & 8;
+                                uint32_t h[8], g[4];
+#pragma unroll
+                                for (int i = 0; i < 8; ++i)
+                                {
+                                    const uint32_t got = __shfl_xor_sync(0xffffffffu, xOdd ? pk[i] : pk[8 + i], 1);
+                                    h[i] = maxBf16x2(xOdd ? pk[8 + i] : pk[i], got);
+                                }
+#pragma unroll
+                                for (int i = 0; i < 4; ++i)
+                                {
+                                    const uint32_t got = __shfl_xor_sync(0xffffffffu, yOdd ? h[i] : h[4 + i], 8);
+                                    g[i] = maxBf16x2(yOdd ? h[4 + i] : h[i], got);
+                                }
+                                // row (y/2)*4 + x/2 of a 32-row piece; 16-byte chunk c lands at c ^ ((r >> 1) & 3)
+                                const int r = (th >> 1) * (kConvTileW / 2) + (tw >> 1);
+                                const int c = (xOdd ? 2 : 0) + (yOdd ? 1 : 0);
+                                stsU4(pieceAddr + r * 64 + ((c ^ ((r >> 1) & 3)) << 4), make_uint4(g[0], g[1], g[2], g[3]));
+                            }
+                            else
+                            {
+                                // row t of a 128 x 64-byte piece; 16-byte chunk c lands at c ^ ((t >> 1) & 3) (SWIZZLE_64B)
+                                const uint32_t rowAddr = pieceAddr + t * 64;
+                                const int sw = (t >> 1) & 3;
+#pragma unroll
+                                for (int c = 0; c < 4; ++c)
+                                    stsU4(rowAddr + ((c ^ sw) << 4),
+                                          make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]));
                             }
                         }
                     }

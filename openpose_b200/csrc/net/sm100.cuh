@@ -245,6 +245,32 @@ namespace sm100
             : "memory");
     }
 
+    // ---------------------------------------------------------------- epilogue helpers
+    __device__ __forceinline__ float4 ldsF4(uint32_t saddr)
+    {
+        float4 v;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
+        return v;
+    }
+    __device__ __forceinline__ void stsU4(uint32_t saddr, uint4 u)
+    {
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(u.x), "r"(u.y), "r"(u.z), "r"(u.w)
+                     : "memory");
+    }
+    // (lo, hi) fp32 -> packed bf16x2, round to nearest even; lo in the low half
+    __device__ __forceinline__ uint32_t packBf16(float lo, float hi)
+    {
+        uint32_t r;
+        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+        return r;
+    }
+    __device__ __forceinline__ uint32_t maxBf16x2(uint32_t a, uint32_t b)
+    {
+        uint32_t r;
+        asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+        return r;
+    }
+
     __device__ __forceinline__ void namedBarrier(uint32_t id, uint32_t threads)
     {
         asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
