@@ -292,7 +292,7 @@ namespace opb
                                 {
 #pragma unroll
                                     for (int kk = 0; kk < kConvBlockK / 16; ++kk)   // 16 bf16 = 32 bytes per MMA along K
-                                        if (kk < steps)
+                                        if (kk < steps && !(p.debugMode & 2))
                                         {
                                             if (PAIR)
                                             {
@@ -408,7 +408,7 @@ namespace opb
                     const int x = tc.x0 + tw, y = tc.y0 + th;
                     const bool inImage = (x < p.W) && (y < p.H);
 #pragma unroll 1
-                    for (int q = half; q < kPieces; q += 2)
+                    for (int q = half; q < kPieces && !(p.debugMode & 1); q += 2)
                     {
                         uint32_t v[32];
                         tmemLoad32(taddr + q * 32, v);
@@ -603,6 +603,8 @@ namespace opb
                               smemBytes))
             OPB_FAIL(OPB200_ERR_UNSUPPORTED, "conv: kernel size too large for the shared-memory pipeline");
         p.aTileBytes = convTileBytes(p.k, p.kxSpan);
+        static const int debugMode = std::getenv("OPB200_CONV_DEBUG") ? std::atoi(std::getenv("OPB200_CONV_DEBUG")) : 0;
+        p.debugMode = debugMode;
         static int configuredDev[64] = {0};   // attribute is per function per device; kSmemLimit covers every k
         int dev = 0;
         OPB_CUDA(cudaGetDevice(&dev));

@@ -90,8 +90,19 @@ namespace opb
             const float ux = divf(vx, norm), uy = divf(vy, norm);
             const float fn = (float)n;
             const float stepx = divf(vx, fn), stepy = divf(vy, fn);
+            // Smallest count that passes `count / n > interMinAbove` in the reference's own float arithmetic (the
+            // quotient is monotonic in count). Once more than n - minCount samples have failed the pair cannot pass
+            // any more and its result no longer depends on the remaining samples: stop reading the maps. Exact.
+            int minCount = (int)mul(c.interMinAbove, fn);
+            minCount = max(0, min(n + 1, minCount));
+            while (minCount <= n && !(divf((float)minCount, fn) > c.interMinAbove))
+                ++minCount;
+            while (minCount > 0 && divf((float)(minCount - 1), fn) > c.interMinAbove)
+                --minCount;
+            const int failsAllowed = n - minCount;
             float sum = 0.f;
             unsigned count = 0;
+            int fails = 0;
             for (int lm = 0; lm < n; lm++)
             {
                 int mx = min(c.w - 1, posIntRound(add(ax, mul((float)lm, stepx))));
@@ -108,6 +119,8 @@ namespace opb
                     sum = add(sum, sc);
                     count++;
                 }
+                else if (++fails > failsAllowed)
+                    break;
             }
             if (divf((float)count, fn) > c.interMinAbove)
                 return divf(sum, (float)count);
