@@ -40,6 +40,8 @@ namespace opb
         int storeBf16;                        // 0: skip the bf16 NHWC store (nobody reads it)
         int poolFused;                        // 1: 2x2/2 MAX pooling in the epilogue; oMap is the pooled blob, box (32, 4, 8, 1)
         int actMode;                          // 1: every slope is 0 (ReLU: add + max); 0: general per-channel slope
+        int reverse;                          // 1: M-tile groups are walked last to first (serpentine order across layers: the
+                                              //    part of the input written last by the previous layer is still in L2)
         int debugMode;                        // experiments only (OPB200_CONV_DEBUG): 1 = epilogue skips math and stores, 2 = no MMAs
         int pairMode;                         // 1: 2-CTA clusters (cta_group::2); bMap box is then (64, BN/2)
     };

@@ -165,8 +165,9 @@ namespace opb
                 uint32_t aPhase = 0, bPhase = 0;
                 for (int work = workStart; work < numWork; work += workStride)
                 {
-                    const int nt = work % p.nTilesN;
-                    const int pair = PAIR ? 2 * (work / p.nTilesN) + (int)ctaRank : work / p.nTilesN;
+                    const int item = p.reverse ? numWork - 1 - work : work;
+                    const int nt = item % p.nTilesN;
+                    const int pair = PAIR ? 2 * (item / p.nTilesN) + (int)ctaRank : item / p.nTilesN;
                     const TileCoord t0 = tileCoord(p, 2 * pair), t1 = tileCoord(p, 2 * pair + 1);
                     int chunk = 0;
                     for (int s = 0; s < p.nSeg; ++s)
@@ -374,8 +375,9 @@ namespace opb
             int lastNt = -1;
             for (int work = workStart; work < numWork; work += workStride)
             {
-                const int nt = work % p.nTilesN;
-                const int pair = PAIR ? 2 * (work / p.nTilesN) + (int)ctaRank : work / p.nTilesN;
+                const int item = p.reverse ? numWork - 1 - work : work;
+                const int nt = item % p.nTilesN;
+                const int pair = PAIR ? 2 * (item / p.nTilesN) + (int)ctaRank : item / p.nTilesN;
                 if (nt != lastNt)
                 {
                     namedBarrier(1, 256);             // everybody is done with the previous table

@@ -747,6 +747,11 @@ namespace opb
         auto viewPtr = [&](const View& v) {
             return net.arena + net.buffers[v.buf].offset + (size_t)v.cOff * 2;
         };
+        // Serpentine tile order: every other conv launch walks its tiles last to first, so a layer starts on the part
+        // of its input the previous launch wrote last (still in L2) instead of the part written first (evicted when a
+        // batch's activations exceed the L2). OPB200_CONV_SERPENTINE=0 turns it off.
+        static const bool serpentine = !(std::getenv("OPB200_CONV_SERPENTINE") && std::atoi(std::getenv("OPB200_CONV_SERPENTINE")) == 0);
+        int convIndex = 0;
         for (auto& op : net.ops)
         {
             if (op.kind == OP_FIRSTCONV)
@@ -756,6 +761,7 @@ namespace opb
             const int h = net.lvH[op.level], w = net.lvW[op.level];
             ConvParams& p = op.cp;
             std::memset(&p, 0, sizeof(p));
+            p.reverse = (serpentine && (convIndex++ & 1) == 0) ? 1 : 0;   // the first-layer kernel runs first to last
             p.tilesX = (w + kConvTileW - 1) / kConvTileW;
             p.tilesY = (h + kConvTileH - 1) / kConvTileH;
             p.numMTiles = N * p.tilesX * p.tilesY;

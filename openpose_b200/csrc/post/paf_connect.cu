@@ -23,7 +23,7 @@ namespace opb
 {
     constexpr int kMaxParts = 25;
     constexpr int kMaxPairs = 26;
-    constexpr int kMatchThreads = 512;
+    constexpr int kMatchThreads = 1024;
     constexpr int kAsmThreads = 256;
 
     struct ModelTables
