@@ -226,6 +226,49 @@ opb200_status opb200_net_read_blob(opb200_net* net, const char* name, float* hos
 opb200_status opb200_net_describe(const char* prototxt, const char* caffemodel, const char* last_blob_name,
                                   char* text, size_t capacity);
 
+/* ---------------------------------------------------------------------------------------------------
+ * Output serialisation -- host only, no CUDA call.
+ * opb200_people_json / _save -- replace op::savePeopleJson and op::PeopleJsonSaver::save
+ *   (reference: include/openpose/filestream/fileStream.hpp:37-45, src/openpose/filestream/fileStream.cpp:20-130
+ *   addKeypointsToJson / addCandidatesToJson, :289-344 savePeopleJson, src/openpose/filestream/jsonOfstream.cpp,
+ *   src/openpose/filestream/peopleJsonSaver.cpp:15-30; wire format doc/02_output.md, version 1.3). Each
+ *   opb200_json_array is one (Array<float>, name) pair of the reference's keypointVector: `people` = getSize(0),
+ *   `per_person` = getSize(1)*getSize(2) (0 for an empty Array, 1 for a 1-D array such as person_id).
+ *   candidates: n_parts part lists, candidate_counts[part] triples (x, y, score) each, concatenated
+ *   (PoseExtractorNet::getCandidatesCopy layout); n_parts = 0 omits "part_candidates" as an empty vector does.
+ *   The bytes equal what the reference's std::ofstream receives (numbers as `ostream << float`, tabs and newlines
+ *   only when human_readable). out = NULL with capacity 0 is a size query; *length is always set.
+ * opb200_people_json_batch -- every frame of a connector batch (keypoints (frames,capacity,parts,3), counts) in one
+ *   pass, each frame the document WPeopleJsonSaver writes for a body-only Datum
+ *   (include/openpose/filestream/wPeopleJsonSaver.hpp:68-97): frame f = out[offsets[f], offsets[f+1]).
+ * opb200_coco_json_* -- replace op::CocoJsonSaver (reference: include/openpose/filestream/cocoJsonSaver.hpp:16-40,
+ *   src/openpose/filestream/cocoJsonSaver.cpp:28-277): open = constructor (same checks, same file names for the
+ *   variants bit mask), record = CocoJsonSaver::record, close = destructor. format = op::CocoJsonFormat
+ *   (0 body, 4 foot, 5 car); pose_model = op::PoseModel.
+ * ------------------------------------------------------------------------------------------------- */
+typedef struct opb200_json_array
+{
+    const char* name;
+    const float* data;   /* host, row-major (people, per_person) */
+    int people;
+    int per_person;
+} opb200_json_array;
+opb200_status opb200_people_json(const opb200_json_array* arrays, int n_arrays, const float* candidates,
+                                 const int* candidate_counts, int n_parts, int human_readable, char* out,
+                                 size_t capacity, size_t* length);
+opb200_status opb200_people_json_save(const char* path, const opb200_json_array* arrays, int n_arrays,
+                                      const float* candidates, const int* candidate_counts, int n_parts,
+                                      int human_readable);
+opb200_status opb200_people_json_batch(const float* keypoints, const int* counts, int frames, int capacity, int parts,
+                                       int human_readable, char* out, size_t out_capacity, size_t* offsets);
+typedef struct opb200_coco_json opb200_coco_json;
+opb200_status opb200_coco_json_open(const char* path, int pose_model, int human_readable, int variants, int format,
+                                    int variant, opb200_coco_json** handle);
+opb200_status opb200_coco_json_record(opb200_coco_json* handle, const float* keypoints, const float* scores,
+                                      int people, int parts, const char* image_name,
+                                      unsigned long long frame_number);
+opb200_status opb200_coco_json_close(opb200_coco_json* handle);
+
 #ifdef __cplusplus
 }
 #endif

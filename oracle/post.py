@@ -280,6 +280,63 @@ class Ref:
                                                  int(producer[0]), int(producer[1])))
         return kp
 
+    def save_people_json(self, keypoint_vector, candidates=None, human_readable=True) -> bytes:
+        """PeopleJsonSaver::save of the reference (own object code) into a temp directory -> the file's bytes."""
+        import tempfile
+        n = len(keypoint_vector)
+        keep, ptrs = [], (_f32p * max(1, n))()
+        dims, ndims = np.zeros((max(1, n), 3), np.int32), np.zeros((max(1, n),), np.int32)
+        names = (C.c_char_p * max(1, n))()
+        for i, (a, name) in enumerate(keypoint_vector):
+            names[i] = name.encode()
+            if a is None or np.size(a) == 0:
+                continue
+            a = np.ascontiguousarray(a, np.float32)
+            keep.append(a)
+            ptrs[i] = _fp(a)
+            ndims[i] = a.ndim
+            dims[i, :a.ndim] = a.shape
+        n_parts = len(candidates) if candidates is not None else 0
+        counts = np.zeros((max(1, n_parts),), np.int32)
+        flat = np.zeros((1, 3), np.float32)
+        if n_parts:
+            parts = [np.asarray(c, np.float32).reshape(-1, 3) for c in candidates]
+            counts[:n_parts] = [c.shape[0] for c in parts]
+            flat = np.ascontiguousarray(np.concatenate(parts + [np.zeros((1, 3), np.float32)], 0), np.float32)
+        self.lib.ref_save_people_json.restype = C.c_int
+        self.lib.ref_save_people_json.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.POINTER(_f32p), _i32p, _i32p,
+                                                  C.POINTER(C.c_char_p), _f32p, _i32p, C.c_int, C.c_int]
+        with tempfile.TemporaryDirectory() as d:
+            self._check(self.lib.ref_save_people_json(d.encode(), b"frame", n, ptrs, _ip(dims), _ip(ndims), names,
+                                                      _fp(flat), _ip(counts), n_parts, int(human_readable)))
+            with open(os.path.join(d, "frame.json"), "rb") as f:
+                return f.read()
+
+    def coco_json(self, frames, image_names, parts, pose_model=0, human_readable=True, variants=1, fmt=0,
+                  variant=0) -> dict:
+        """CocoJsonSaver of the reference over `frames` = [(keypoints (P,parts,3), scores (P))] -> {file suffix: bytes}."""
+        import tempfile
+        people = np.array([np.asarray(k).reshape(-1, parts, 3).shape[0] for k, _ in frames], np.int32)
+        kp = np.ascontiguousarray(np.concatenate([np.asarray(k, np.float32).reshape(-1, parts, 3) for k, _ in frames]
+                                                 + [np.zeros((1, parts, 3), np.float32)], 0))
+        sc = np.ascontiguousarray(np.concatenate([np.asarray(s, np.float32).reshape(-1) for _, s in frames]
+                                                 + [np.zeros((1,), np.float32)], 0))
+        names = (C.c_char_p * max(1, len(frames)))()
+        for i, nme in enumerate(image_names):
+            names[i] = nme.encode()
+        self.lib.ref_coco_json.restype = C.c_int
+        self.lib.ref_coco_json.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, _f32p,
+                                           _i32p, C.c_int, C.POINTER(C.c_char_p)]
+        with tempfile.TemporaryDirectory() as d:
+            path = os.path.join(d, "coco.json")
+            self._check(self.lib.ref_coco_json(path.encode(), pose_model, int(human_readable), variants, fmt, variant,
+                                               len(frames), _fp(kp), _fp(sc), _ip(people), parts, names))
+            out = {}
+            for fn in sorted(os.listdir(d)):
+                with open(os.path.join(d, fn), "rb") as f:
+                    out[fn] = f.read()
+            return out
+
     def nms(self, heat, thr, channels, off=(0.5, 0.5), max_peaks=MAX_PEAKS, peaks=None) -> np.ndarray:
         heat = np.ascontiguousarray(heat, np.float32)
         _, h, w = heat.shape

@@ -16,6 +16,9 @@
 //       core/keypointScaler.cpp, utilities/keypoint.cpp -- all compiled unmodified; keypoint.cpp's renderer sees a
 //       type-only opencv2/imgproc stand-in written by oracle/Makefile and is never called): the Array<T> copy / move /
 //       slice constructors, clone, getVolume(a, b) of array.cpp:165-280,470-500 (storage plumbing only).
+//   (6) for the output serialisation (filestream/fileStream.cpp, jsonOfstream.cpp, cocoJsonSaver.cpp, peopleJsonSaver.cpp,
+//       fileSaver.cpp, utilities/fileSystem.cpp -- all compiled unmodified; fileStream.cpp's image / FileStorage functions
+//       see a type-only opencv2/highgui stand-in and are never called): Matrix(const void*) / getConstCvMat (never run).
 // Nothing here restates reference arithmetic: nms / PAF scoring / assembly all run in the
 // reference's own object code.
 #include <cstdio>
@@ -30,6 +33,8 @@
 #include <openpose/core/keepTopNPeople.hpp>
 #include <openpose/core/keypointScaler.hpp>
 #include <openpose/face/faceDetector.hpp>
+#include <openpose/filestream/cocoJsonSaver.hpp>
+#include <openpose/filestream/peopleJsonSaver.hpp>
 #include <openpose/hand/handDetector.hpp>
 #include <openpose/net/bodyPartConnectorBase.hpp>
 #include <openpose/net/nmsBase.hpp>
@@ -39,6 +44,9 @@ namespace op
 {
     // (2) Matrix(): an empty handle is all Array<T> needs.
     Matrix::Matrix() {}
+    // (6) only referenced by fileStream.cpp's image / FileStorage helpers, which the oracle never calls
+    Matrix::Matrix(const void*) { std::abort(); }
+    const void* Matrix::getConstCvMat() const { std::abort(); }
 
     // (1) Array<T> members. Storage semantics: row-major, owned by a shared_ptr<T[]>.
     template<typename T>
@@ -88,7 +96,7 @@ namespace op
     {
         if ((unsigned)index < mSize.size())
             return mSize[index];
-        return 0;
+        return !mSize.empty();   // array.cpp:425-437 (Matlab style): 0 for an empty Array, 1 past the last dimension
     }
 
     template<typename T>
@@ -421,6 +429,74 @@ extern "C"
             scaler.scale(a, scaleInputToOutput, scaleNetToOutput, op::Point<int>{producerW, producerH});
             if (!a.empty())
                 std::memcpy(kp, a.getConstPtr(), sizeof(float) * a.getVolume());
+            return 0;
+        }
+        catch (const std::exception& e)
+        {
+            std::snprintf(gErr, sizeof(gErr), "%s", e.what());
+            return -1;
+        }
+    }
+
+    // PeopleJsonSaver::save, src/openpose/filestream/peopleJsonSaver.cpp:15-30 -> savePeopleJson, fileStream.cpp:306-344.
+    // arrays: nArrays x (data, dims[3], nDims) with nDims in {0 (empty Array), 1, 3}; file = dir/fileName.json
+    int ref_save_people_json(const char* dir, const char* fileName, int nArrays, const float* const* data,
+                             const int* dims, const int* nDims, const char* const* names, const float* cand,
+                             const int* candCounts, int nParts, int humanReadable)
+    {
+        try
+        {
+            std::vector<std::pair<op::Array<float>, std::string>> kv;
+            for (int v = 0; v < nArrays; ++v)
+            {
+                op::Array<float> a;
+                if (nDims[v] > 0)
+                {
+                    std::vector<int> sz(dims + 3 * v, dims + 3 * v + nDims[v]);
+                    a.reset(sz);
+                    if (a.getVolume() > 0)
+                        std::memcpy(a.getPtr(), data[v], sizeof(float) * a.getVolume());
+                }
+                kv.emplace_back(a, names[v]);
+            }
+            std::vector<std::vector<std::array<float, 3>>> candidates((size_t)nParts);
+            const float* p = cand;
+            for (int part = 0; part < nParts; ++part)
+                for (int c = 0; c < candCounts[part]; ++c, p += 3)
+                    candidates[part].push_back(std::array<float, 3>{p[0], p[1], p[2]});
+            const op::PeopleJsonSaver saver{dir};
+            saver.save(kv, candidates, fileName, humanReadable != 0);
+            return 0;
+        }
+        catch (const std::exception& e)
+        {
+            std::snprintf(gErr, sizeof(gErr), "%s", e.what());
+            return -1;
+        }
+    }
+
+    // CocoJsonSaver (constructor, record per frame, destructor), src/openpose/filestream/cocoJsonSaver.cpp:28-277.
+    // kp: frames concatenated, people[f] x parts x 3 each; scores likewise; names: one image name per frame.
+    int ref_coco_json(const char* path, int poseModel, int humanReadable, int variants, int format, int variant,
+                      int nFrames, const float* kp, const float* scores, const int* people, int parts,
+                      const char* const* names)
+    {
+        try
+        {
+            op::CocoJsonSaver saver{path, (op::PoseModel)poseModel, humanReadable != 0, variants,
+                                    (op::CocoJsonFormat)format, variant};
+            for (int f = 0; f < nFrames; ++f)
+            {
+                op::Array<float> sc;
+                if (people[f] > 0)
+                {
+                    sc.reset(people[f]);
+                    std::memcpy(sc.getPtr(), scores, sizeof(float) * people[f]);
+                }
+                saver.record(peopleArray(kp, people[f], parts), sc, names[f], (unsigned long long)f);
+                kp += (size_t)people[f] * parts * 3;
+                scores += people[f];
+            }
             return 0;
         }
         catch (const std::exception& e)
