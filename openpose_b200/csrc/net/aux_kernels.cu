@@ -113,7 +113,8 @@ namespace opb
 
     __global__ void __launch_bounds__(256) nhwcToNchwKernel(float* __restrict__ dst,
                                                             const __nv_bfloat16* __restrict__ src, int N, int C, int H,
-                                                            int W, int srcStride, int dstC, int dstOff)
+                                                            int W, int srcStride, int dstC, int dstOff,
+                                                            long long strideN, long long strideY)
     {
         const long long total = (long long)N * C * H * W;
         for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -124,18 +125,24 @@ namespace opb
             const int c = (int)((i / ((long long)W * H)) % C);
             const int n = (int)(i / ((long long)W * H * C));
             dst[(((long long)n * dstC + dstOff + c) * H + y) * W + x] =
-                __bfloat162float(src[(((long long)n * H + y) * W + x) * srcStride + c]);
+                __bfloat162float(src[n * strideN + y * strideY + (long long)x * srcStride + c]);
         }
     }
 
+    // strideN / strideY: element strides of the frame and row indices (0 = dense [n][y][x] pixels of srcStride channels)
     opb200_status launchNhwcToNchw(float* dst, const void* src, int N, int C, int H, int W, int srcStride, int dstC,
-                                   int dstOff, cudaStream_t st)
+                                   int dstOff, cudaStream_t st, long long strideN, long long strideY)
     {
+        if (strideN == 0 && strideY == 0)
+        {
+            strideY = (long long)W * srcStride;
+            strideN = strideY * H;
+        }
         const long long total = (long long)N * C * H * W;
         const long long want = (total + 255) / 256;
         const int blocks = (int)(want < 148 * 16 ? want : 148 * 16);
         nhwcToNchwKernel<<<blocks > 0 ? blocks : 1, 256, 0, st>>>(dst, static_cast<const __nv_bfloat16*>(src), N, C, H,
-                                                                 W, srcStride, dstC, dstOff);
+                                                                 W, srcStride, dstC, dstOff, strideN, strideY);
         OPB_LAUNCH_CHECK();
         return OPB200_OK;
     }

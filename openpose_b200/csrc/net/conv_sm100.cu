@@ -409,6 +409,7 @@ namespace opb
                         tmemBase + (acc * 2 + j) * Cfg::kAccStride + ((uint32_t)(quad * 32) << 16);
                     const int x = tc.x0 + tw, y = tc.y0 + th;
                     const bool inImage = (x < p.W) && (y < p.H);
+                    const bool isSeparator = p.flatPitch != 0 && (x % p.flatPitch) == p.flatW;
 #pragma unroll 1
                     for (int q = half; q < kPieces && !(p.debugMode & 1); q += 2)
                     {
@@ -452,12 +453,22 @@ namespace opb
                         if (p.out32 != nullptr && inImage)
                         {
                             const int cBase = nt * BN + q * 32;
-                            float* o = p.out32 + (((size_t)tc.n * p.out32C + p.out32Off + cBase) * p.H + y) * p.W + x;
-                            const size_t plane = (size_t)p.H * p.W;
+                            int fn = tc.n, fx = x, fw = p.W;
+                            if (p.flatPitch)           // flat level: x runs over all frames and their separators
+                            {
+                                fn = x / p.flatPitch;
+                                fx = x - fn * p.flatPitch;
+                                fw = p.flatW;
+                            }
+                            float* o = p.out32 + (((size_t)fn * p.out32C + p.out32Off + cBase) * p.H + y) * fw + fx;
+                            const size_t plane = (size_t)p.H * fw;
+                            if (fx < fw && fn < (p.flatPitch ? p.flatN : p.N))   // not a separator column
+                            {
 #pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                if (cBase + i < p.cout)
-                                    o[i * plane] = f[i];
+                                for (int i = 0; i < 32; ++i)
+                                    if (cBase + i < p.cout)
+                                        o[i * plane] = f[i];
+                            }
                         }
                         if (p.storeBf16 | p.poolFused)
                         {
@@ -465,6 +476,12 @@ namespace opb
 #pragma unroll
                             for (int i = 0; i < 16; ++i)
                                 pk[i] = packBf16(f[2 * i], f[2 * i + 1]);
+                            if (isSeparator)           // flat level: the zero column between two frames stays zero
+                            {
+#pragma unroll
+                                for (int i = 0; i < 16; ++i)
+                                    pk[i] = 0u;
+                            }
                             const uint32_t pieceAddr = smemAddr(sOut + q * (kConvBlockM * 64));
                             if (p.poolFused)
                             {
@@ -521,7 +538,14 @@ namespace opb
                             const int sx = p.poolFused ? tc.x0 >> 1 : tc.x0, sy = p.poolFused ? tc.y0 >> 1 : tc.y0;
                             for (int q = half; q < kPieces; q += 2)
                                 if (nt * BN + q * 32 < p.cout)
-                                    tmaStore4d(&p.oMap, sOut + q * (kConvBlockM * 64), nt * BN + q * 32, sx, sy, tc.n);
+                                {
+                                    const void* src = sOut + q * (kConvBlockM * 64);
+                                    const int c0 = nt * BN + q * 32;
+                                    if (p.poolFused && p.poolOutFlat)   // per-frame map of a flat level: (c, x, n, y)
+                                        tmaStore4d(&p.oMap, src, c0, sx, tc.n, sy);
+                                    else
+                                        tmaStore4d(&p.oMap, src, c0, sx, sy, tc.n);
+                                }
                             tmaStoreCommit();
                         }
                     }

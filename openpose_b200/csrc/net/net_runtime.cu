@@ -85,6 +85,29 @@ namespace opb
         return OPB200_OK;
     }
 
+    opb200_status makeFlatStoreMap(CUtensorMap* m, const void* base, int C, int W, int H, int N, int pitchW, int strideC,
+                                   int boxC, int TW, int TH)
+    {
+        EncodeTiledFn fn = encodeTiled();
+        if (!fn)
+            OPB_FAIL(OPB200_ERR_CUDA, "cuTensorMapEncodeTiled is unavailable (driver too old?)");
+        const cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)N, (cuuint64_t)H};
+        const cuuint64_t strides[3] = {(cuuint64_t)strideC * 2, (cuuint64_t)strideC * 2 * pitchW,
+                                       (cuuint64_t)strideC * 2 * pitchW * N};
+        const cuuint32_t box[4] = {(cuuint32_t)boxC, (cuuint32_t)TW, 1, (cuuint32_t)TH};
+        const cuuint32_t es[4] = {1, 1, 1, 1};
+        const CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, es,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS)
+        {
+            setError("cuTensorMapEncodeTiled(flat store C=%d W=%d H=%d N=%d pitch=%d stride=%d) failed: %d", C, W, H, N,
+                     pitchW, strideC, (int)r);
+            return OPB200_ERR_CUDA;
+        }
+        return OPB200_OK;
+    }
+
     // ------------------------------------------------------------------------------------------------
     // plan
     // ------------------------------------------------------------------------------------------------
@@ -159,6 +182,7 @@ namespace opb
         // shape-dependent state
         int N = 0, H = 0, W = 0;
         std::vector<int> lvH, lvW;
+        std::vector<int> lvFlat;   // per level: 1 = frame-interleaved layout [y][n][x of W + 1][c] (conv_params.h)
         uint8_t* arena = nullptr;
         size_t arenaBytes = 0;
         float* dInput = nullptr;
@@ -723,8 +747,36 @@ namespace opb
             total += (bytes + 1023) / 1024 * 1024;
             return at;
         };
+        // Flat levels (conv_params.h): only where every reader and writer of the level's buffers is the conv kernel
+        // (TMA loads, TMA stores, fused pooled stores) or the fp32 converter, and where it saves M tiles.
+        const bool flatEnabled = !(std::getenv("OPB200_CONV_FLAT") && std::atoi(std::getenv("OPB200_CONV_FLAT")) == 0);
+        net.lvFlat.assign(net.levels.size(), 0);
+        for (size_t l = 0; l < net.levels.size(); ++l)
+        {
+            const int w = net.lvW[l], h = net.lvH[l];
+            const long long tilesPlain = (long long)N * ((w + kConvTileW - 1) / kConvTileW);
+            const long long tilesFlat = ((long long)N * (w + 1) + kConvTileW - 1) / kConvTileW;
+            bool ok = flatEnabled && N > 1 && tilesFlat < tilesPlain && h > 0;
+            for (const auto& op : net.ops)
+            {
+                const bool touches = op.level == (int)l || op.outLevel == (int)l || (op.poolFused && op.poolLevel == (int)l);
+                if (!touches)
+                    continue;
+                if (op.kind == OP_CONV)
+                {
+                    if (op.level == (int)l && op.poolFused)
+                        ok = false;   // a flat level whose conv also pools: pooled windows would cross frame borders
+                }
+                else if (op.kind != OP_CONVERT)
+                    ok = false;       // patch / first conv / stand-alone pooling address pixels as [n][y][x]
+            }
+            net.lvFlat[l] = ok ? 1 : 0;
+        }
         for (auto& b : net.buffers)
-            b.offset = carve((size_t)N * net.lvH[b.level] * net.lvW[b.level] * b.C * 2);
+        {
+            const int w = net.lvW[b.level] + (net.lvFlat[b.level] ? 1 : 0);
+            b.offset = carve((size_t)N * net.lvH[b.level] * w * b.C * 2);
+        }
         net.inputBytes = (size_t)N * net.inputC * H * W * 4;
         net.outBytes = (size_t)N * net.outC * net.lvH[net.outLevel] * net.lvW[net.outLevel] * 4;
         const size_t inOff = carve(net.inputBytes), outOff = carve(net.outBytes);
@@ -762,12 +814,17 @@ namespace opb
             ConvParams& p = op.cp;
             std::memset(&p, 0, sizeof(p));
             p.reverse = (serpentine && (convIndex++ & 1) == 0) ? 1 : 0;   // the first-layer kernel runs first to last
-            p.tilesX = (w + kConvTileW - 1) / kConvTileW;
+            const bool flat = net.lvFlat[op.level] != 0;
+            const int kw = flat ? N * (w + 1) : w, kn = flat ? 1 : N;   // the image the kernel sees
+            p.flatPitch = flat ? w + 1 : 0;
+            p.flatW = w;
+            p.flatN = N;
+            p.tilesX = (kw + kConvTileW - 1) / kConvTileW;
             p.tilesY = (h + kConvTileH - 1) / kConvTileH;
-            p.numMTiles = N * p.tilesX * p.tilesY;
+            p.numMTiles = kn * p.tilesX * p.tilesY;
             p.H = h;
-            p.W = w;
-            p.N = N;
+            p.W = kw;
+            p.N = kn;
             p.k = op.k;
             p.pad = op.pad;
             // 3x3: one halo box per chunk serves all nine taps; larger kernels keep one box per filter column
@@ -799,7 +856,7 @@ namespace opb
                     const int valid = std::min(kConvBlockK, op.in[s].C - c * kConvBlockK);
                     p.chunkSteps[chunk] = (uint8_t)((valid + 15) / 16);
                 }
-                const opb200_status st = makeActivationMap(&p.aMap[s], viewPtr(op.in[s]), op.in[s].C, w, h, N,
+                const opb200_status st = makeActivationMap(&p.aMap[s], viewPtr(op.in[s]), op.in[s].C, kw, h, kn,
                                                            net.buffers[op.in[s].buf].C, kConvBlockK, p.boxW,
                                                            kConvTileH + op.k - 1, true);
                 if (st != OPB200_OK)
@@ -816,12 +873,17 @@ namespace opb
             if (st != OPB200_OK)
                 return st;
             p.poolFused = op.poolFused ? 1 : 0;
-            if (op.poolFused)   // the pooled blob, one (32 ch, 4, 8) box per tile
+            p.poolOutFlat = (op.poolFused && net.lvFlat[op.poolLevel]) ? 1 : 0;
+            if (op.poolFused && p.poolOutFlat)   // pooled blob on a flat level: per-frame store map
+                st = makeFlatStoreMap(&p.oMap, viewPtr(op.poolOut), op.poolOut.C, net.lvW[op.poolLevel],
+                                      net.lvH[op.poolLevel], N, net.lvW[op.poolLevel] + 1,
+                                      net.buffers[op.poolOut.buf].C, 32, kConvTileW / 2, kConvTileH / 2);
+            else if (op.poolFused)   // the pooled blob, one (32 ch, 4, 8) box per tile
                 st = makeActivationMap(&p.oMap, viewPtr(op.poolOut), op.poolOut.C, net.lvW[op.poolLevel],
                                        net.lvH[op.poolLevel], N, net.buffers[op.poolOut.buf].C, 32, kConvTileW / 2,
                                        kConvTileH / 2, false);
-            else
-                st = makeActivationMap(&p.oMap, viewPtr(op.out), op.out.C, w, h, N, net.buffers[op.out.buf].C, 32,
+            else   // (flat level: one image of width N * (W + 1); the epilogue writes zeros into the separator columns)
+                st = makeActivationMap(&p.oMap, viewPtr(op.out), op.out.C, kw, h, kn, net.buffers[op.out.buf].C, 32,
                                        kConvTileW, kConvTileH, false);
             if (st != OPB200_OK)
                 return st;
@@ -867,8 +929,12 @@ namespace opb
                                   net.buffers[op.out.buf].C, st);
                 break;
             case OP_CONVERT:
-                s = launchNhwcToNchw(net.dOut32, viewPtr(op.in[0]), net.N, op.in[0].C, h, w,
-                                     net.buffers[op.in[0].buf].C, net.outC, op.out32Off, st);
+            {
+                const long long sc = net.buffers[op.in[0].buf].C;
+                const bool flat = net.lvFlat[op.level] != 0;
+                s = launchNhwcToNchw(net.dOut32, viewPtr(op.in[0]), net.N, op.in[0].C, h, w, (int)sc, net.outC,
+                                     op.out32Off, st, flat ? (w + 1) * sc : 0, flat ? (long long)net.N * (w + 1) * sc : 0);
+            }
                 break;
             }
             if (s != OPB200_OK)
@@ -1095,8 +1161,11 @@ extern "C" opb200_status opb200_net_read_blob(opb200_net* n, const char* name, f
     opb200_status s = OPB200_OK;
     for (const View& v : b.segs)
     {
+        const long long sc = net.buffers[v.buf].C;
+        const bool flat = net.lvFlat[b.level] != 0;
         s = launchNhwcToNchw(tmp, net.arena + net.buffers[v.buf].offset + (size_t)v.cOff * 2, net.N, v.C, h, w,
-                             net.buffers[v.buf].C, b.C, cOff, nullptr);
+                             (int)sc, b.C, cOff, nullptr, flat ? (w + 1) * sc : 0,
+                             flat ? (long long)net.N * (w + 1) * sc : 0);
         if (s != OPB200_OK)
             break;
         cOff += v.C;

@@ -112,6 +112,26 @@ def test_openpose_models_within_tolerance(cuda, model, shape):
     net.close()
 
 
+def test_flat_level_layout_is_bit_identical(cuda, monkeypatch):
+    """Frame-interleaved levels (conv_params.h: tiles run across frame borders, zero separator columns) change which
+    tile computes a pixel, not its arithmetic: outputs and intermediate blobs equal the plain layout bit for bit."""
+    proto, cm, _ = ref_net.build("body_25", 1234)
+    x = synth.frames_to_net_input(synth.frames(5, 112, 176, 9))    # level 3 = 14 x 22: 5*3 = 15 column tiles -> 15 < ... flat
+    outs = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("OPB200_CONV_FLAT", flag)
+        net = NetB200(proto, cm)
+        net.initializationOnThread()
+        net.forwardPass(x)
+        out = net.getOutputBlobArray().cpu().numpy().copy()
+        net.forwardPass(torch.from_numpy(x).to(cuda))              # graph replay on the same buffers
+        assert np.array_equal(out, net.getOutputBlobArray().cpu().numpy())
+        outs[flag] = (out, net.readBlob("conv4_4_CPM"), net.readBlob("Mconv7_stage0_L2"))
+        net.close()
+    for a, b in zip(outs["0"], outs["1"]):
+        assert a.shape == b.shape and np.array_equal(a, b)
+
+
 def test_reshape_device_input_and_repeatability(cuda):
     proto, cm, ref = ref_net.build("body_25", 1234)
     net = NetB200(proto, cm)
