@@ -50,6 +50,18 @@ def load_peaks():
     return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback")
 
 
+def conv_traffic(batch: int):
+    """dram__bytes_read.sum + dram__bytes_write.sum over the conv launches of one step, from the committed ncu capture
+    of this command at the same batch (profiles/r01_conv_traffic.json); None when there is no capture for this batch."""
+    p = os.path.join(ROOT, "profiles", "r01_conv_traffic.json")
+    try:
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["dram_bytes_per_step"]) if int(d["batch"]) == batch else None
+    except (OSError, ValueError, KeyError):
+        return None
+
+
 class ClockSampler:
     """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -376,7 +388,7 @@ def run_gpu(args):
         achieved = CONV_GFLOP_PER_FRAME * B / conv_ms          # GFLOP/ms = TFLOP/s
         roof = {"bound": "tensor", "kernel": "conv_igemm_tcgen05 (all conv launches of one step)",
                 "achieved": achieved, "peak": peaks_tbl["tf_sustained"], "unit": "TFLOP/s",
-                "frac": achieved / peaks_tbl["tf_sustained"], "traffic": None,
+                "frac": achieved / peaks_tbl["tf_sustained"], "traffic": conv_traffic(B),
                 "peak_source": peaks_tbl["source"] + " sustained bf16", "launch_ms": conv_ms}
     else:
         rms = stage_avg["resize"]
