@@ -1,3 +1,3 @@
-python -m pytest tests/test_net_gpu.py -x -q 2>&1 | tail -2
-ncu --metrics gpu__time_duration.sum --clock-control none -k regex:firstConv -c 3 --csv --log-file gpurun_out/fc.csv python bench.py --stages net --steps 1 --warmup 1 --no-cpu > /dev/null 2>&1
-grep firstConv gpurun_out/fc.csv | awk -F'","' '{print $NF}'
+for r in 1 2 3; do for m in 0 1; do
+OPB200_CONV_FLAT=$m python bench.py --stages net --no-cpu --steps 40 --warmup 5 2>&1 | tail -1 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('flat=$m', round(d['value']), d['stages_ms'], d['clocks']['sm_mhz'])"
+done; done
