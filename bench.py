@@ -406,7 +406,7 @@ def run_gpu(args):
     if world == 1 and not args.no_cpu:
         cpu = cpu_baseline(args, host_in)
 
-    launches = (net.launches_per_step() if have_net else 0) + (4 if post is not None else 0)
+    launches = (net.launches_per_step() if have_net else 0) + (5 if post is not None else 0)
     line = {
         "metric": "BODY_25 656x368 frames/s", "value": value, "unit": "frames/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,

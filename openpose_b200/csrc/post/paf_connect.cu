@@ -62,6 +62,8 @@ namespace opb
         const float* peaks;  // (N, parts, maxPeaks+1, 3)
         float* cube;         // optional (N, pairs, maxPeaks, maxPeaks)
         int* conn;           // (N, pairs, 1 + 3*maxPeaks): count, i[], j[], scoreBits[]
+        unsigned long long* candKeys;   // (N, pairs, maxPeaks^2): candidate keys of pafCandKernel, unordered
+        int* candCount;                 // (N, pairs)
         float* outKeypoints; // (N, capacity, parts, 3)
         float* outScores;    // (N, capacity)
         int* outCount;       // (N)
@@ -162,7 +164,39 @@ namespace opb
     }
 
     // ------------------------------------------------------------------------------------------------
-    // Kernel A: scores + sort + greedy matching for one (limb, frame).
+    // Kernel A0: candidate scores of every (limb, frame) at full occupancy. The line integral is a chain of dependent
+    // gathers, so it wants as many resident warps as the SM holds; the sort of kernel A needs 128 KB of shared memory
+    // per CTA and would cap that at one CTA per SM. Candidates (score > 1e-6) go to a per-(limb, frame) list in
+    // arbitrary order: their keys are distinct, so the sort of kernel A makes the result deterministic.
+    // ------------------------------------------------------------------------------------------------
+    constexpr int kCandThreads = 256;
+    __global__ void __launch_bounds__(kCandThreads) pafCandKernel(const ConnectArgs c)
+    {
+        const int pair = blockIdx.y, n = blockIdx.z;
+        const int mp = c.maxPeaks, po = 3 * (mp + 1);
+        const float* pk = c.peaks + (size_t)n * c.t.parts * po;
+        const float* A = pk + c.t.pairTable[2 * pair] * po;
+        const float* B = pk + c.t.pairTable[2 * pair + 1] * po;
+        const int nA = posIntRound(A[0]), nB = posIntRound(B[0]);
+        const int t = blockIdx.x * kCandThreads + threadIdx.x;
+        if (t >= nA * nB)
+            return;
+        const size_t hw = (size_t)c.h * c.w;
+        const float* mapX = c.heat + ((size_t)n * c.heatChannels + c.t.parts + 1 + c.t.mapIdx[2 * pair]) * hw;
+        const float* mapY = c.heat + ((size_t)n * c.heatChannels + c.t.parts + 1 + c.t.mapIdx[2 * pair + 1]) * hw;
+        const int i = t / nB + 1, j = t - (i - 1) * nB + 1;
+        const float s = pafScore<OPB200_SEMANTICS_CPU>(A + 3 * i, B + 3 * j, mapX, mapY, c);
+        if ((double)s > 1e-6) // reference: bodyPartConnectorBase.cpp:317
+        {
+            const size_t slot = (size_t)n * c.t.pairs + pair;
+            const int pos = atomicAdd(c.candCount + slot, 1);
+            c.candKeys[slot * mp * mp + pos] =
+                ((unsigned long long)__float_as_uint(s) << 16) | ((unsigned)i << 8) | (unsigned)j;
+        }
+    }
+
+    // ------------------------------------------------------------------------------------------------
+    // Kernel A: (scores, unless kernel A0 ran) + sort + greedy matching for one (limb, frame).
     // ------------------------------------------------------------------------------------------------
     __global__ void __launch_bounds__(kMatchThreads) pafMatchKernel(const ConnectArgs c)
     {
@@ -198,16 +232,27 @@ namespace opb
         const size_t hw = (size_t)c.h * c.w;
         const float* mapX = c.heat + ((size_t)n * c.heatChannels + c.t.parts + 1 + c.t.mapIdx[2 * pair]) * hw;
         const float* mapY = c.heat + ((size_t)n * c.heatChannels + c.t.parts + 1 + c.t.mapIdx[2 * pair + 1]) * hw;
-        for (int t = threadIdx.x; t < nA * nB; t += kMatchThreads)
+        if (c.candKeys != nullptr)
         {
-            const int i = t / nB + 1, j = t - (i - 1) * nB + 1;
-            const float s = pafScore<OPB200_SEMANTICS_CPU>(A + 3 * i, B + 3 * j, mapX, mapY, c);
-            if ((double)s > 1e-6) // reference: bodyPartConnectorBase.cpp:317
-            {
-                const int pos = atomicAdd(&nCand, 1);
-                keys[pos] = ((unsigned long long)__float_as_uint(s) << 16) | ((unsigned)i << 8) | (unsigned)j;
-            }
+            const size_t slot = (size_t)n * c.t.pairs + pair;
+            const int have = c.candCount[slot];
+            const unsigned long long* src = c.candKeys + slot * mp * mp;
+            for (int t = threadIdx.x; t < have; t += kMatchThreads)
+                keys[t] = src[t];
+            if (threadIdx.x == 0)
+                nCand = have;
         }
+        else
+            for (int t = threadIdx.x; t < nA * nB; t += kMatchThreads)
+            {
+                const int i = t / nB + 1, j = t - (i - 1) * nB + 1;
+                const float s = pafScore<OPB200_SEMANTICS_CPU>(A + 3 * i, B + 3 * j, mapX, mapY, c);
+                if ((double)s > 1e-6) // reference: bodyPartConnectorBase.cpp:317
+                {
+                    const int pos = atomicAdd(&nCand, 1);
+                    keys[pos] = ((unsigned long long)__float_as_uint(s) << 16) | ((unsigned)i << 8) | (unsigned)j;
+                }
+            }
         __syncthreads();
         const int cand = nCand;
         int sortN = 1;
@@ -865,7 +910,10 @@ extern "C" size_t opb200_connect_scratch_bytes(const opb200_connect_params* p, i
             keys <<= 1;
         return (size_t)n_frames * (sizeof(float) * cells + sizeof(opb::ConnKey) * keys) + 256;
     }
-    return sizeof(int) * (size_t)n_frames * t->pairs * (1 + 3 * (size_t)p->max_peaks);
+    // connection lists, then the candidate counters and key lists of pafCandKernel
+    const size_t conn = (sizeof(int) * (size_t)n_frames * t->pairs * (1 + 3 * (size_t)p->max_peaks) + 255) & ~(size_t)255;
+    const size_t counts = (sizeof(int) * (size_t)n_frames * t->pairs + 255) & ~(size_t)255;
+    return conn + counts + sizeof(unsigned long long) * (size_t)n_frames * t->pairs * p->max_peaks * p->max_peaks;
 }
 
 extern "C" opb200_status opb200_paf_scores(float* cube, const float* heat, const float* peaks,
@@ -880,6 +928,8 @@ extern "C" opb200_status opb200_paf_scores(float* cube, const float* heat, const
     c.heat = heat;
     c.peaks = peaks;
     c.cube = cube;
+    c.candKeys = nullptr;
+    c.candCount = nullptr;
     const dim3 grid((c.maxPeaks * c.maxPeaks + 255) / 256, c.t.pairs, heat_shape[0]);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (p->semantics == OPB200_SEMANTICS_CPU)
@@ -904,6 +954,8 @@ extern "C" opb200_status opb200_connect(float* out_keypoints, float* out_scores,
     c.heat = heat;
     c.peaks = peaks;
     c.cube = nullptr;
+    c.candKeys = nullptr;
+    c.candCount = nullptr;
     c.conn = static_cast<int*>(scratch);
     c.outKeypoints = out_keypoints;
     c.outScores = out_scores;
@@ -936,6 +988,16 @@ extern "C" opb200_status opb200_connect(float* out_keypoints, float* out_scores,
         return OPB200_OK;
     }
 
+    {
+        const size_t connBytes = (sizeof(int) * (size_t)nFrames * c.t.pairs * (1 + 3 * (size_t)c.maxPeaks) + 255) & ~(size_t)255;
+        const size_t countBytes = (sizeof(int) * (size_t)nFrames * c.t.pairs + 255) & ~(size_t)255;
+        c.candCount = reinterpret_cast<int*>(static_cast<unsigned char*>(scratch) + connBytes);
+        c.candKeys = reinterpret_cast<unsigned long long*>(static_cast<unsigned char*>(scratch) + connBytes + countBytes);
+        OPB_CUDA(cudaMemsetAsync(c.candCount, 0, sizeof(int) * (size_t)nFrames * c.t.pairs, st));
+        const dim3 grid((c.maxPeaks * c.maxPeaks + kCandThreads - 1) / kCandThreads, c.t.pairs, nFrames);
+        pafCandKernel<<<grid, kCandThreads, 0, st>>>(c);
+        OPB_LAUNCH_CHECK();
+    }
     const size_t smemA = sizeof(unsigned long long) * (size_t)c.sortCap;
     OPB_CUDA(cudaFuncSetAttribute(pafMatchKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemA));
     pafMatchKernel<<<dim3(c.t.pairs, nFrames), kMatchThreads, smemA, st>>>(c);
