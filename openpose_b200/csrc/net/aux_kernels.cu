@@ -170,6 +170,14 @@ namespace opb
         return *reinterpret_cast<uint32_t*>(&v);
     }
 
+    // (lo, hi) fp32 -> packed bf16x2 with max(x, 0) folded into the conversion
+    __device__ __forceinline__ uint32_t packBf16Relu(float lo, float hi)
+    {
+        uint32_t r;
+        asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+        return r;
+    }
+
     constexpr int kFirstWarps = 8;
     constexpr int kFirstPitch = 144;   // bytes per staged pixel row (128 + 16: conflict-free 16-byte reads)
 
@@ -276,30 +284,22 @@ namespace opb
 #pragma unroll
                 for (int t = 0; t < 2; ++t)
                 {
-                    float c[4] = {0.f, 0.f, 0.f, 0.f};
+                    float c[4] = {b2.x, b2.y, b2.x, b2.y};   // the accumulator starts at the bias
                     mmaSyncBf16(c, a[t][0], wb[nt][0][0], wb[nt][0][1]);
                     mmaSyncBf16(c, a[t][1], wb[nt][1][0], wb[nt][1][1]);
-                    float o[4];
-                    o[0] = c[0] + b2.x;
-                    o[1] = c[1] + b2.y;
-                    o[2] = c[2] + b2.x;
-                    o[3] = c[3] + b2.y;
-                    if (relu)
+                    uint32_t lo, hi;
+                    if (relu)                                 // max(x, 0) folded into the bf16 conversion
                     {
-                        o[0] = fmaxf(o[0], 0.f);
-                        o[1] = fmaxf(o[1], 0.f);
-                        o[2] = fmaxf(o[2], 0.f);
-                        o[3] = fmaxf(o[3], 0.f);
+                        lo = packBf16Relu(c[0], c[1]);
+                        hi = packBf16Relu(c[2], c[3]);
                     }
                     else
                     {
-                        o[0] = o[0] > 0.f ? o[0] : o[0] * s2.x;
-                        o[1] = o[1] > 0.f ? o[1] : o[1] * s2.y;
-                        o[2] = o[2] > 0.f ? o[2] : o[2] * s2.x;
-                        o[3] = o[3] > 0.f ? o[3] : o[3] * s2.y;
+                        lo = packBf16(c[0] > 0.f ? c[0] : c[0] * s2.x, c[1] > 0.f ? c[1] : c[1] * s2.y);
+                        hi = packBf16(c[2] > 0.f ? c[2] : c[2] * s2.x, c[3] > 0.f ? c[3] : c[3] * s2.y);
                     }
-                    *reinterpret_cast<uint32_t*>(st + (t * 16 + g) * kFirstPitch + nt * 16 + q * 4) = packBf16(o[0], o[1]);
-                    *reinterpret_cast<uint32_t*>(st + (t * 16 + g + 8) * kFirstPitch + nt * 16 + q * 4) = packBf16(o[2], o[3]);
+                    *reinterpret_cast<uint32_t*>(st + (t * 16 + g) * kFirstPitch + nt * 16 + q * 4) = lo;
+                    *reinterpret_cast<uint32_t*>(st + (t * 16 + g + 8) * kFirstPitch + nt * 16 + q * 4) = hi;
                 }
             }
             __syncwarp();

@@ -427,10 +427,11 @@ namespace opb
 #pragma unroll
                             for (int i = 0; i < 8; ++i)
                             {
-                                f[4 * i + 0] = fmaxf(__uint_as_float(v[4 * i + 0]) + b4[i].x, 0.f);
-                                f[4 * i + 1] = fmaxf(__uint_as_float(v[4 * i + 1]) + b4[i].y, 0.f);
-                                f[4 * i + 2] = fmaxf(__uint_as_float(v[4 * i + 2]) + b4[i].z, 0.f);
-                                f[4 * i + 3] = fmaxf(__uint_as_float(v[4 * i + 3]) + b4[i].w, 0.f);
+                                // (the max with 0 happens in the bf16 conversion below; ReLU layers have no fp32 output)
+                                f[4 * i + 0] = __uint_as_float(v[4 * i + 0]) + b4[i].x;
+                                f[4 * i + 1] = __uint_as_float(v[4 * i + 1]) + b4[i].y;
+                                f[4 * i + 2] = __uint_as_float(v[4 * i + 2]) + b4[i].z;
+                                f[4 * i + 3] = __uint_as_float(v[4 * i + 3]) + b4[i].w;
                             }
                         }
                         else
@@ -473,9 +474,18 @@ namespace opb
                         if (p.storeBf16 | p.poolFused)
                         {
                             uint32_t pk[16];           // channels (2i, 2i+1) as packed bf16
+                            if (p.actMode == 1)
+                            {
 #pragma unroll
-                            for (int i = 0; i < 16; ++i)
-                                pk[i] = packBf16(f[2 * i], f[2 * i + 1]);
+                                for (int i = 0; i < 16; ++i)
+                                    pk[i] = packBf16Relu(f[2 * i], f[2 * i + 1]);
+                            }
+                            else
+                            {
+#pragma unroll
+                                for (int i = 0; i < 16; ++i)
+                                    pk[i] = packBf16(f[2 * i], f[2 * i + 1]);
+                            }
                             if (isSeparator)           // flat level: the zero column between two frames stays zero
                             {
 #pragma unroll

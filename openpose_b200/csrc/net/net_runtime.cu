@@ -843,6 +843,8 @@ namespace opb
             for (int co = 0; co < op.cout; ++co)
                 if (op.hostSlope[co] != 0.f)
                     p.actMode = 0;
+            if (op.out32Off >= 0)
+                p.actMode = 0;   // the fast ReLU path clamps in the bf16 conversion only: fp32 outputs take the general one
             p.out32 = op.out32Off >= 0 ? net.dOut32 : nullptr;
             p.out32C = net.outC;
             p.out32Off = op.out32Off >= 0 ? op.out32Off : 0;

@@ -264,6 +264,13 @@ namespace sm100
         asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
         return r;
     }
+    // the same with max(x, 0) folded into the conversion (ReLU layers)
+    __device__ __forceinline__ uint32_t packBf16Relu(float lo, float hi)
+    {
+        uint32_t r;
+        asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+        return r;
+    }
     __device__ __forceinline__ uint32_t maxBf16x2(uint32_t a, uint32_t b)
     {
         uint32_t r;

@@ -1,3 +1,2 @@
-for r in 1 2 3; do for m in 0 1; do
-OPB200_CONV_FLAT=$m python bench.py --stages net --no-cpu --steps 40 --warmup 5 2>&1 | tail -1 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('flat=$m', round(d['value']), d['stages_ms'], d['clocks']['sm_mhz'])"
-done; done
+python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+python bench.py --no-cpu --steps 20 --warmup 3 2>&1 | tail -1 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print(round(d['value']), round(d['e2e']['value']), d['stages_ms'])"

@@ -99,6 +99,32 @@ def test_connect_cuda_semantics_matches_reference(port, cuda, case):
         assert np.array_equal(gs[0, :n].cpu().numpy(), sc)
 
 
+def test_connect_maximum_number_of_candidates(port, cuda):
+    """A uniform PAF field pointing to +x with even parts on the left half and odd parts on the right: every pair of a
+    limb that runs even -> odd passes the line integral: 127 x 127 = 16129 candidates, the most a limb can have (full
+    candidate lists of pafCandKernel, full 16384-key sort). Result must equal the oracle's std::sort + greedy matching."""
+    h, w, parts, n = 96, 160, 25, 127
+    rng = np.random.default_rng(17)
+    maps = np.zeros((78, h, w), np.float32)
+    maps[26::2] = 0.5                                   # x components of every limb's PAF
+    peaks = np.zeros((parts, 128, 3), np.float32)
+    for p in range(parts):
+        lo, hi = (2, w // 2 - 8) if p % 2 == 0 else (w // 2 + 8, w - 3)
+        peaks[p, 0, 0] = n
+        peaks[p, 1:n + 1, 0] = rng.uniform(lo, hi, n)
+        peaks[p, 1:n + 1, 1] = rng.uniform(2, h - 3, n)
+        peaks[p, 1:n + 1, 2] = rng.uniform(0.1, 1.0, n)
+    cube = port.pair_scores(maps, peaks, 0, mode=MODE_CPU)
+    assert int((cube > 1e-6).sum(axis=(1, 2)).max()) > 8192
+    kp, sc, _ = port.connect(maps, peaks, 0, scale=1.0)
+    params = post.make_connect_params(0, scale_factor=1.0)
+    gk, gs, gc = post.connect_body_parts_gpu(torch.from_numpy(maps[None]).to(cuda), torch.from_numpy(peaks[None]).to(cuda),
+                                             params, capacity=4096)
+    n = int(gc[0].item())
+    assert n == kp.shape[0] and n > 0
+    assert np.array_equal(gk[0, :n].cpu().numpy(), kp) and np.array_equal(gs[0, :n].cpu().numpy(), sc)
+
+
 def test_connect_cuda_semantics_batch(port, cuda):
     cases = [POST_CASES[1], POST_CASES[5], POST_CASES[3]]
     maps = np.stack([make_case(c)[0] for c in cases])
