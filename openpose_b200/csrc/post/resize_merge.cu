@@ -13,6 +13,7 @@
 // to the non-fused evaluation of cuda.hu (the oracle, oracle/post_oracle.c:opo_resize_merge).
 #include "../common.cuh"
 #include "bicubic.cuh"
+#include <algorithm>
 
 namespace opb
 {
@@ -116,7 +117,7 @@ namespace opb
     // output rows). Per scale: x-pass of the needed source rows into shared memory, then a 1-D cubic per pixel.
     // ------------------------------------------------------------------------------------------------
     constexpr int kGenThreads = 256;
-    constexpr int kBandRows = 8;
+    constexpr int kBandRows = 16;
     constexpr int kMaxTmpRows = 14;
 
     struct MergeArgs
@@ -127,90 +128,132 @@ namespace opb
         int nScales, ht, wt, maxTmpRows;
     };
 
-    __global__ void __launch_bounds__(kGenThreads) resizeMergeKernel(float* __restrict__ dst, const MergeArgs a)
+    // Every thread owns whole output COLUMNS of the band: per scale it runs the x-pass of its column over the few
+    // source rows the band touches (values kept in a private shared-memory column: no barrier), then walks the band's
+    // rows; the y taps / offsets of a row are block-uniform and come from a table built once per block, and the
+    // A, B, C polynomial coefficients of cuda.hu are reused while consecutive rows read the same four source rows.
+    // Every output value is formed by the reference's operations in the reference's order (bit-exact), only the
+    // sharing changes.
+    __global__ void __launch_bounds__(kGenThreads, 3) resizeMergeKernel(float* __restrict__ dst, const MergeArgs a)
     {
-        extern __shared__ float tmp[]; // [maxTmpRows][wt]
+        __shared__ float tmp[kMaxTmpRows * kGenThreads];                  // [source row of the band][thread]
+        __shared__ int rowTap[OPB200_MAX_SCALES][kBandRows][4];           // clamped source rows of an output row
+        __shared__ float rowDy[OPB200_MAX_SCALES][kBandRows];
+        __shared__ int rowNew[OPB200_MAX_SCALES][kBandRows];              // 1: other source rows than the row above
+        __shared__ int rowLo[OPB200_MAX_SCALES], rowCnt[OPB200_MAX_SCALES];
         const size_t planeIdx = blockIdx.y;
         const int yBand = blockIdx.x * kBandRows;
         const int rowsHere = min(kBandRows, a.ht - yBand);
-        const int nPix = rowsHere * a.wt;
-        constexpr int kSlots = 24; // pixels per thread kept in registers
-        float acc[kSlots];
-#pragma unroll
-        for (int k = 0; k < kSlots; k++)
-            acc[k] = 0.f;
-
-        for (int pixBase = 0; pixBase < nPix; pixBase += kSlots * kGenThreads)
+        for (int t = threadIdx.x; t < a.nScales * kBandRows; t += blockDim.x)
         {
+            const int i = t / kBandRows, yy = t - i * kBandRows;
+            int yi[4];
+            float dy;
+            taps(yi, dy, srcCoord(yBand + min(yy, rowsHere - 1), a.scaleH[i]), a.hs[i]);
 #pragma unroll
-            for (int k = 0; k < kSlots; k++)
-                acc[k] = 0.f;
+            for (int r = 0; r < 4; r++)
+                rowTap[i][yy][r] = yi[r];
+            rowDy[i][yy] = dy;
+            if (yy == 0)
+                rowLo[i] = yi[0];
+            if (yy == rowsHere - 1)
+                rowCnt[i] = yi[3];     // last source row for now, turned into a count below
+        }
+        __syncthreads();
+        if (threadIdx.x < a.nScales)
+            rowCnt[threadIdx.x] = rowCnt[threadIdx.x] - rowLo[threadIdx.x] + 1;
+        for (int t = threadIdx.x; t < a.nScales * kBandRows; t += blockDim.x)
+        {
+            const int i = t / kBandRows, yy = t - i * kBandRows;
+            bool fresh = yy == 0;
+            for (int r = 0; r < 4 && !fresh; r++)
+                fresh = rowTap[i][yy][r] != rowTap[i][yy - 1][r];
+            rowNew[i][yy] = fresh ? 1 : 0;
+        }
+        __syncthreads();
+
+        float* __restrict__ dp = dst + planeIdx * (size_t)a.ht * a.wt + (size_t)yBand * a.wt;
+        const float cnt = (float)a.nScales;
+        float* mine = tmp + threadIdx.x;
+        for (int x = threadIdx.x; x < a.wt; x += blockDim.x)   // (runtime loop: the unrolled body is per column)
+        {
+            float acc[kBandRows];
+#pragma unroll
+            for (int yy = 0; yy < kBandRows; yy++)
+                acc[yy] = 0.f;
+#pragma unroll 1
             for (int i = 0; i < a.nScales; i++)
             {
                 const float* __restrict__ sp = a.src[i] + planeIdx * a.hs[i] * a.ws[i];
-                int yi[4];
-                float dyDummy;
-                taps(yi, dyDummy, srcCoord(yBand, a.scaleH[i]), a.hs[i]);
-                const int rlo = yi[0];
-                taps(yi, dyDummy, srcCoord(yBand + rowsHere - 1, a.scaleH[i]), a.hs[i]);
-                const int rhi = yi[3];
-                const int nrows = rhi - rlo + 1;
-                const bool staged = nrows <= a.maxTmpRows; // block-uniform
+                const int rlo = rowLo[i], nrows = rowCnt[i];
+                const bool staged = nrows <= a.maxTmpRows;   // block-uniform
+                int xi[4];
+                float dx;
+                taps(xi, dx, srcCoord(x, a.scaleW[i]), a.ws[i]);
                 if (staged)
                 {
-                    __syncthreads();
-                    for (int t = threadIdx.x; t < nrows * a.wt; t += kGenThreads)
+                    // all loads of up to 7 source rows are issued before the first cubic: one L2 round trip, not 7
+                    const float* r = sp + (size_t)rlo * a.ws[i];
+#pragma unroll 1
+                    for (int j0 = 0; j0 < nrows; j0 += 7)
                     {
-                        const int j = t / a.wt, x = t - j * a.wt;
-                        int xi[4];
-                        float dx;
-                        taps(xi, dx, srcCoord(x, a.scaleW[i]), a.ws[i]);
-                        const float* r = sp + (size_t)(rlo + j) * a.ws[i];
-                        tmp[t] = cubic1d(__ldg(r + xi[0]), __ldg(r + xi[1]), __ldg(r + xi[2]), __ldg(r + xi[3]), dx);
-                    }
-                    __syncthreads();
-                }
+                        float v[7][4];
 #pragma unroll
-                for (int k = 0; k < kSlots; k++)
+                        for (int u = 0; u < 7; u++)
+                        {
+                            const float* ru = r + (size_t)min(j0 + u, nrows - 1) * a.ws[i];
+#pragma unroll
+                            for (int e = 0; e < 4; e++)
+                                v[u][e] = __ldg(ru + xi[e]);
+                        }
+#pragma unroll
+                        for (int u = 0; u < 7; u++)
+                            if (j0 + u < nrows)
+                                mine[(j0 + u) * kGenThreads] = cubic1d(v[u][0], v[u][1], v[u][2], v[u][3], dx);
+                    }
+                }
+                float A = 0.f, Bc = 0.f, Cc = 0.f, v1 = 0.f;
+#pragma unroll
+                for (int yy = 0; yy < kBandRows; yy++)
                 {
-                    const int p = pixBase + k * kGenThreads + threadIdx.x;
-                    if (p < nPix)
+                    if (yy < rowsHere)
                     {
-                        const int yy = p / a.wt, x = p - yy * a.wt;
-                        float dy;
-                        taps(yi, dy, srcCoord(yBand + yy, a.scaleH[i]), a.hs[i]);
-                        float t4[4];
-                        if (staged)
+                        if (rowNew[i][yy])   // block-uniform
                         {
-#pragma unroll
-                            for (int r = 0; r < 4; r++)
-                                t4[r] = tmp[(yi[r] - rlo) * a.wt + x];
-                        }
-                        else
-                        {
-                            int xi[4];
-                            float dx;
-                            taps(xi, dx, srcCoord(x, a.scaleW[i]), a.ws[i]);
-#pragma unroll
-                            for (int r = 0; r < 4; r++)
+                            const int y0 = rowTap[i][yy][0], y1 = rowTap[i][yy][1], y2 = rowTap[i][yy][2],
+                                      y3 = rowTap[i][yy][3];
+                            float t0, t1, t2, t3;
+                            if (staged)
                             {
-                                const float* rr = sp + (size_t)yi[r] * a.ws[i];
-                                t4[r] = cubic1d(__ldg(rr + xi[0]), __ldg(rr + xi[1]), __ldg(rr + xi[2]), __ldg(rr + xi[3]), dx);
+                                t0 = mine[(y0 - rlo) * kGenThreads];
+                                t1 = mine[(y1 - rlo) * kGenThreads];
+                                t2 = mine[(y2 - rlo) * kGenThreads];
+                                t3 = mine[(y3 - rlo) * kGenThreads];
                             }
+                            else
+                            {
+                                const float* r0 = sp + (size_t)y0 * a.ws[i];
+                                const float* r1 = sp + (size_t)y1 * a.ws[i];
+                                const float* r2 = sp + (size_t)y2 * a.ws[i];
+                                const float* r3 = sp + (size_t)y3 * a.ws[i];
+                                t0 = cubic1d(__ldg(r0 + xi[0]), __ldg(r0 + xi[1]), __ldg(r0 + xi[2]), __ldg(r0 + xi[3]), dx);
+                                t1 = cubic1d(__ldg(r1 + xi[0]), __ldg(r1 + xi[1]), __ldg(r1 + xi[2]), __ldg(r1 + xi[3]), dx);
+                                t2 = cubic1d(__ldg(r2 + xi[0]), __ldg(r2 + xi[1]), __ldg(r2 + xi[2]), __ldg(r2 + xi[3]), dx);
+                                t3 = cubic1d(__ldg(r3 + xi[0]), __ldg(r3 + xi[1]), __ldg(r3 + xi[2]), __ldg(r3 + xi[3]), dx);
+                            }
+                            A = cubicA(t0, t1, t2, t3);
+                            Bc = cubicB(t0, t1, t2, t3);
+                            Cc = cubicC(t0, t2);
+                            v1 = t1;
                         }
-                        acc[k] = add(acc[k], cubic1d(t4[0], t4[1], t4[2], t4[3], dy));
+                        acc[yy] = add(acc[yy], cubicEval(A, Bc, Cc, v1, rowDy[i][yy]));
                     }
                 }
             }
-            float* __restrict__ dp = dst + planeIdx * (size_t)a.ht * a.wt + (size_t)yBand * a.wt;
-            const float cnt = (float)a.nScales;
 #pragma unroll
-            for (int k = 0; k < kSlots; k++)
-            {
-                const int p = pixBase + k * kGenThreads + threadIdx.x;
-                if (p < nPix)
-                    dp[p] = a.nScales == 1 ? acc[k] : divf(acc[k], cnt);
-            }
+            for (int yy = 0; yy < kBandRows; yy++)
+                if (yy < rowsHere)
+                    dp[(size_t)yy * a.wt + x] = a.nScales == 1 ? acc[yy] : divf(acc[yy], cnt);
         }
     }
 
@@ -300,14 +343,9 @@ extern "C" opb200_status opb200_resize_merge(float* dst, const float* const* src
         a.hs[i] = src_shapes[i][2];
         a.ws[i] = src_shapes[i][3];
     }
-    const size_t rowBytes = sizeof(float) * (size_t)wt;
-    int rows = (int)((200u * 1024u) / rowBytes);
-    rows = rows > kMaxTmpRows ? kMaxTmpRows : rows;
-    a.maxTmpRows = rows >= 4 ? rows : 0;
-    const size_t smem = rowBytes * (size_t)a.maxTmpRows;
-    OPB_CUDA(cudaFuncSetAttribute(resizeMergeKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem > 0 ? smem : 4)));
+    a.maxTmpRows = kMaxTmpRows;
     const dim3 grid((ht + kBandRows - 1) / kBandRows, (unsigned)planes);
-    resizeMergeKernel<<<grid, kGenThreads, smem, st>>>(dst, a);
+    resizeMergeKernel<<<grid, kGenThreads, 0, st>>>(dst, a);
     OPB_LAUNCH_CHECK();
     return OPB200_OK;
 }

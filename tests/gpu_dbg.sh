@@ -1,2 +1,2 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-python bench.py --no-cpu --steps 20 --warmup 3 2>&1 | tail -1 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print(round(d['value']), round(d['e2e']['value']), d['stages_ms'])"
+python -m pytest tests/test_post_gpu.py tests/test_extractor_gpu.py tests/test_shim_gpu.py -x -q 2>&1 | tail -3
+PYTHONPATH=. python tests/bench_kernels.py 2>&1 | grep -E "4 scales|resize x8"
