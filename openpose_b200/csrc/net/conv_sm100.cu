@@ -23,6 +23,7 @@
 #include "conv_params.h"
 #include "sm100.cuh"
 #include <cuda_bf16.h>
+#include <cstdio>
 #include <cstdlib>
 
 namespace opb
@@ -55,6 +56,14 @@ namespace opb
     };
     constexpr int kAuxBytes = 2048;
     static_assert(sizeof(ConvAux) <= kAuxBytes, "aux block too large");
+
+    // Debug timeline (OPB200_CONV_TRACE): clock64 stamps of CTA 0's roles per work item, printed by the kernel itself.
+    __device__ unsigned long long gConvTrace[16 * 16 + 2];
+    __device__ __forceinline__ void traceStamp(bool on, int slot, int work)
+    {
+        if (on && work < 16)
+            reinterpret_cast<volatile unsigned long long*>(gConvTrace)[slot * 16 + work] = clock64();
+    }
 
     struct TileCoord
     {
@@ -97,7 +106,8 @@ namespace opb
         const uint32_t groupPitch = (uint32_t)p.boxW * 128u;                         // bytes between pixel rows
         uint8_t* sA = smem;                                         // aStages x (tile0 | tile1)
         uint8_t* sB = sA + p.aStages * aStageBytes;                 // bStages x (BN x 128 B)
-        uint8_t* sOut = sB + p.bStages * kBStageBytes;              // staging for the TMA store
+        const int bStageBytes = p.bGroup * kBStageBytes;            // one weight stage = bGroup K blocks
+        uint8_t* sOut = sB + p.bStages * bStageBytes;               // staging for the TMA store
         ConvAux* aux = reinterpret_cast<ConvAux*>(sOut + Cfg::kStagingBytes);
 
         // Programmatic dependent launch: let the next layer's CTAs start their prologue on SMs this grid has
@@ -154,92 +164,105 @@ namespace opb
         // everything above touched only kernel parameters, smem and TMEM; from here on we read the previous
         // layer's output and overwrite buffers it may still be reading
         asm volatile("griddepcontrol.wait;" ::: "memory");
+        const bool traceOn = (p.debugMode & 4) && blockIdx.x == 0;
+        if (traceOn && threadIdx.x == 0)
+            reinterpret_cast<volatile unsigned long long*>(gConvTrace)[256] = clock64();
 
         if (warp == 0)
         {
-            // ===================================== TMA producer ======================================
-            // the whole (converged) warp runs the loop and waits; the elected lane issues
+            // ============================ TMA producer: activations (A) ===============================
+            // the whole (converged) warp runs the loop and waits; the elected lane issues. Activations and weights
+            // have their own producer warps: the weight ring is short (it follows the MMAs closely), and a single
+            // producer blocked on it could not request the NEXT item's activation boxes early enough -- a box takes
+            // 3-4 k cycles to arrive when the TMA queue is busy (OPB200_CONV_TRACE timeline).
             const bool leader = electOne();
+            int as = 0;
+            uint32_t aPhase = 0;
+            for (int work = workStart; work < numWork; work += workStride)
             {
-                int as = 0, bs = 0;
-                uint32_t aPhase = 0, bPhase = 0;
-                for (int work = workStart; work < numWork; work += workStride)
-                {
-                    const int item = p.reverse ? numWork - 1 - work : work;
-                    const int nt = item % p.nTilesN;
-                    const int pair = PAIR ? 2 * (item / p.nTilesN) + (int)ctaRank : item / p.nTilesN;
-                    const TileCoord t0 = tileCoord(p, 2 * pair), t1 = tileCoord(p, 2 * pair + 1);
-                    int chunk = 0;
-                    for (int s = 0; s < p.nSeg; ++s)
-                        for (int c = 0; c < p.segChunks[s]; ++c, ++chunk)
-                            for (int kx = 0; kx < p.k; ++kx)
+                const int item = p.reverse ? numWork - 1 - work : work;
+                const int pair = PAIR ? 2 * (item / p.nTilesN) + (int)ctaRank : item / p.nTilesN;
+                const TileCoord t0 = tileCoord(p, 2 * pair), t1 = tileCoord(p, 2 * pair + 1);
+                const int wi = (work - workStart) / workStride;
+                traceStamp(traceOn && leader, 0, wi);
+                for (int s = 0; s < p.nSeg; ++s)
+                    for (int c = 0; c < p.segChunks[s]; ++c)
+                        for (int kx = 0; kx < p.k; kx += p.kxSpan)
+                        {
+                            // one box serves kxSpan filter columns (and all k filter rows)
+                            mbarWait(&aux->aEmpty[as], aPhase ^ 1);
+                            uint8_t* dst = sA + as * aStageBytes;
+                            if (leader)
                             {
-                                if (kx % p.kxSpan == 0)
+                                if (PAIR)
                                 {
-                                    // one box serves kxSpan filter columns (and all k filter rows)
-                                    mbarWait(&aux->aEmpty[as], aPhase ^ 1);
-                                    uint8_t* dst = sA + as * aStageBytes;
-                                    if (leader)
-                                    {
-                                        if (PAIR)
-                                        {
-                                            // both CTAs' boxes are counted on the leader CTA's barrier
-                                            const uint32_t bar = mapaShared(smemAddr(&aux->aFull[as]), 0);
-                                            if (ctaRank == 0)
-                                                mbarExpectTx(&aux->aFull[as], 4 * boxBytes);
-                                            tmaLoad4dPair(dst, &p.aMap[s], bar, c * kConvBlockK, t0.x0 + kx - p.pad,
-                                                          t0.y0 - p.pad, t0.n);
-                                            tmaLoad4dPair(dst + p.aTileBytes, &p.aMap[s], bar, c * kConvBlockK,
-                                                          t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
-                                        }
-                                        else
-                                        {
-                                            mbarExpectTx(&aux->aFull[as], 2 * boxBytes);
-                                            tmaLoad4d(dst, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
-                                                      t0.x0 + kx - p.pad, t0.y0 - p.pad, t0.n);
-                                            tmaLoad4d(dst + p.aTileBytes, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
-                                                      t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
-                                        }
-                                    }
-                                    __syncwarp();
-                                    if (++as == p.aStages)
-                                    {
-                                        as = 0;
-                                        aPhase ^= 1;
-                                    }
+                                    // both CTAs' boxes are counted on the leader CTA's barrier
+                                    const uint32_t bar = mapaShared(smemAddr(&aux->aFull[as]), 0);
+                                    if (ctaRank == 0)
+                                        mbarExpectTx(&aux->aFull[as], 4 * boxBytes);
+                                    tmaLoad4dPair(dst, &p.aMap[s], bar, c * kConvBlockK, t0.x0 + kx - p.pad,
+                                                  t0.y0 - p.pad, t0.n);
+                                    tmaLoad4dPair(dst + p.aTileBytes, &p.aMap[s], bar, c * kConvBlockK,
+                                                  t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
                                 }
-                                const int kb0 = (chunk * p.k + kx) * p.k;
-                                if (p.bResident && work != workStart)
-                                    continue;          // the whole weight tile already sits in shared memory
-                                for (int ky = 0; ky < p.k; ++ky)
+                                else
                                 {
-                                    mbarWait(&aux->bEmpty[bs], bPhase ^ 1);
-                                    if (leader)
-                                    {
-                                        if (PAIR)
-                                        {
-                                            // this CTA's half of the Cout tile (bMap box = BN/2 rows)
-                                            if (ctaRank == 0)
-                                                mbarExpectTx(&aux->bFull[bs], Cfg::kBBytes);
-                                            tmaLoad2dPair(sB + bs * kBStageBytes, &p.bMap,
-                                                          mapaShared(smemAddr(&aux->bFull[bs]), 0),
-                                                          (kb0 + ky) * kConvBlockK, nt * BN + (int)ctaRank * (BN / 2));
-                                        }
-                                        else
-                                        {
-                                            mbarExpectTx(&aux->bFull[bs], Cfg::kBBytes);
-                                            tmaLoad2d(sB + bs * Cfg::kBBytes, &p.bMap, &aux->bFull[bs],
-                                                      (kb0 + ky) * kConvBlockK, nt * BN);
-                                        }
-                                    }
-                                    __syncwarp();
-                                    if (++bs == p.bStages)
-                                    {
-                                        bs = 0;
-                                        bPhase ^= 1;
-                                    }
+                                    mbarExpectTx(&aux->aFull[as], 2 * boxBytes);
+                                    tmaLoad4d(dst, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
+                                              t0.x0 + kx - p.pad, t0.y0 - p.pad, t0.n);
+                                    tmaLoad4d(dst + p.aTileBytes, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
+                                              t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
                                 }
                             }
+                            __syncwarp();
+                            if (++as == p.aStages)
+                            {
+                                as = 0;
+                                aPhase ^= 1;
+                            }
+                        }
+                traceStamp(traceOn && leader, 1, wi);
+            }
+        }
+        else if (warp == 3)
+        {
+            // ============================== TMA producer: weights (B) =================================
+            const bool leader = electOne();
+            int bs = 0;
+            uint32_t bPhase = 0;
+            for (int work = workStart; work < numWork; work += workStride)
+            {
+                if (p.bResident && work != workStart)
+                    break;                 // the whole weight tile already sits in shared memory
+                const int item = p.reverse ? numWork - 1 - work : work;
+                const int nt = item % p.nTilesN;
+                const int kBlocks = p.chunksTotal * p.k * p.k;
+                // one box = bGroup filter rows (consecutive K blocks) of this Cout tile
+                for (int kb = 0; kb < kBlocks; kb += p.bGroup)
+                {
+                    mbarWait(&aux->bEmpty[bs], bPhase ^ 1);
+                    if (leader)
+                    {
+                        if (PAIR)
+                        {
+                            // this CTA's half of the Cout tile (bMap box = BN/2 rows)
+                            if (ctaRank == 0)
+                                mbarExpectTx(&aux->bFull[bs], p.bGroup * Cfg::kBBytes);
+                            tmaLoad3dPair(sB + bs * bStageBytes, &p.bMap, mapaShared(smemAddr(&aux->bFull[bs]), 0), 0,
+                                          nt * BN + (int)ctaRank * (BN / 2), kb);
+                        }
+                        else
+                        {
+                            mbarExpectTx(&aux->bFull[bs], p.bGroup * Cfg::kBBytes);
+                            tmaLoad3d(sB + bs * bStageBytes, &p.bMap, &aux->bFull[bs], 0, nt * BN, kb);
+                        }
+                    }
+                    __syncwarp();
+                    if (++bs == p.bStages)
+                    {
+                        bs = 0;
+                        bPhase ^= 1;
+                    }
                 }
             }
         }
@@ -259,8 +282,11 @@ namespace opb
                 const uint64_t kyStep = (uint64_t)(p.boxW * 8);         // one box pixel row down, in 16-byte units
                 for (int work = workStart; work < numWork; work += workStride)
                 {
+                    const int wi = (work - workStart) / workStride;
+                    traceStamp(traceOn && leader, 2, wi);
                     mbarWait(&aux->tmemEmpty[acc], accPhase ^ 1);
                     tcFenceAfter();
+                    traceStamp(traceOn && leader, 3, wi);
                     const uint32_t tmemD0 = tmemBase + (acc * 2) * Cfg::kAccStride;
                     const uint32_t tmemD1 = tmemD0 + Cfg::kAccStride;
                     int chunk = 0, axInChunk = 0;
@@ -274,6 +300,8 @@ namespace opb
                             ++chunk;
                         }
                         mbarWait(&aux->aFull[as], aPhase);
+                        if (ax == 0)
+                            traceStamp(traceOn && leader, 4, wi);
                         // tap (kxi, ky) = the 16 pixel rows starting at box pixel (kxi, ky): 8-pixel groups groupPitch
                         // bytes apart, the first one (ky * boxW + kxi) * 128 bytes into the box. Descriptors are built
                         // once per stage and advanced by adding 16-byte units to the start-address field.
@@ -284,11 +312,16 @@ namespace opb
                         {
                             uint64_t aDesc0 = aBase0 + (uint64_t)(kxi * 8);
                             uint64_t aDesc1 = aBase1 + (uint64_t)(kxi * 8);
+                            int kyInGroup = 0;
                             for (int ky = 0; ky < p.k; ++ky)
                             {
-                                mbarWait(&aux->bFull[bs], bPhase);
-                                tcFenceAfter();
-                                const uint64_t bDesc = bBase + (uint64_t)(bs * (kBStageBytes >> 4));
+                                if (kyInGroup == 0)
+                                {
+                                    mbarWait(&aux->bFull[bs], bPhase);
+                                    tcFenceAfter();
+                                }
+                                const uint64_t bDesc = bBase + (uint64_t)((bs * p.bGroup + kyInGroup) * (kBStageBytes >> 4));
+                                const bool groupDone = ++kyInGroup == p.bGroup;
                                 if (leader)
                                 {
 #pragma unroll
@@ -306,7 +339,7 @@ namespace opb
                                                 mmaBf16(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
                                             }
                                         }
-                                    if (!p.bResident)   // weight slot free (in both CTAs) once these MMAs retire
+                                    if (groupDone && !p.bResident)   // weight slot free (in both CTAs) once these MMAs retire
                                     {
                                         if (PAIR)
                                             mmaCommitPair(&aux->bEmpty[bs]);
@@ -317,10 +350,14 @@ namespace opb
                                 __syncwarp();
                                 first = 1;
                                 // resident weights: the slots are never recycled, their (only) phase stays complete
-                                if (++bs == p.bStages)
+                                if (groupDone)
                                 {
-                                    bs = 0;
-                                    bPhase ^= p.bResident ? 0u : 1u;
+                                    kyInGroup = 0;
+                                    if (++bs == p.bStages)
+                                    {
+                                        bs = 0;
+                                        bPhase ^= p.bResident ? 0u : 1u;
+                                    }
                                 }
                                 aDesc0 += kyStep;
                                 aDesc1 += kyStep;
@@ -340,6 +377,7 @@ namespace opb
                             aPhase ^= 1;
                         }
                     }
+                    traceStamp(traceOn && leader, 5, wi);
                     if (leader)                                   // both accumulators complete -> epilogue(s)
                     {
                         if (PAIR)
@@ -389,8 +427,12 @@ namespace opb
                     lastNt = nt;
                     namedBarrier(1, 256);
                 }
+                const int wi = (work - workStart) / workStride;
                 mbarWait(&aux->tmemFull[acc], accPhase);
                 tcFenceAfter();
+                traceStamp(traceOn && et == 0, 6, wi);
+                traceStamp(traceOn && lane == 0 && wi == 1, 15, warp - 4);
+                bool released = false;
 #pragma unroll 1
                 for (int j = 0; j < 2; ++j)
                 {
@@ -405,6 +447,7 @@ namespace opb
                             tmaStoreWaitRead0();
                         namedBarrier(halfBar, 128);
                     }
+                    traceStamp(traceOn && et == 0, 8 + 2 * j, wi);
                     const uint32_t taddr =
                         tmemBase + (acc * 2 + j) * Cfg::kAccStride + ((uint32_t)(quad * 32) << 16);
                     const int x = tc.x0 + tw, y = tc.y0 + th;
@@ -538,10 +581,25 @@ namespace opb
                             }
                         }
                     }
+                    traceStamp(traceOn && et == 0, 9 + 2 * j, wi);
+                    traceStamp(traceOn && lane == 0 && wi == 1, j ? 12 : 14, warp - 4);
+                    if (j == 1 || mt + 1 >= p.numMTiles)
+                    {
+                        // all TMEM reads of this thread are complete (wait::ld above): hand both accumulators back NOW,
+                        // before the stores -- a TMA store queues behind every load the producer has in flight
+                        // (thousands of cycles), and the MMA issuer needs only the accumulator, not the stores
+                        tcFenceBefore();
+                        if (PAIR)   // the MMA issuer lives in the leader CTA: both CTAs' epilogues report to its barrier
+                            mbarArriveCluster(mapaShared(smemAddr(&aux->tmemEmpty[acc]), 0));
+                        else
+                            mbarArrive(&aux->tmemEmpty[acc]);
+                        released = true;
+                    }
                     if (p.storeBf16 | p.poolFused)
                     {
                         fenceProxyAsyncShared();
                         namedBarrier(halfBar, 128);
+                        traceStamp(traceOn && lane == 0 && wi == 1 && j == 1, 13, warp - 4);
                         if (issuer)
                         {
                             // pooled: oMap describes the pooled blob with a (32 ch, 4, 8) box
@@ -560,12 +618,15 @@ namespace opb
                         }
                     }
                 }
-                // all TMEM reads of this thread are complete (wait::ld above): hand both accumulators back
-                tcFenceBefore();
-                if (PAIR)   // the MMA issuer lives in the leader CTA: both CTAs' epilogues report to its barrier
-                    mbarArriveCluster(mapaShared(smemAddr(&aux->tmemEmpty[acc]), 0));
-                else
-                    mbarArrive(&aux->tmemEmpty[acc]);
+                if (!released)   // no tile of this item belongs to this CTA (ragged end of a quad)
+                {
+                    tcFenceBefore();
+                    if (PAIR)
+                        mbarArriveCluster(mapaShared(smemAddr(&aux->tmemEmpty[acc]), 0));
+                    else
+                        mbarArrive(&aux->tmemEmpty[acc]);
+                }
+                traceStamp(traceOn && et == 0, 7, wi);
                 if (++acc == 2)
                 {
                     acc = 0;
@@ -576,6 +637,26 @@ namespace opb
                 tmaStoreWaitAll();
         }
         tcFenceBefore();
+        if (traceOn)
+        {
+            __syncthreads();
+            if (threadIdx.x == 0)
+            {
+                const volatile unsigned long long* tr = reinterpret_cast<volatile unsigned long long*>(gConvTrace);
+                const unsigned long long z = tr[256];
+                const int n = (numWork - workStart + workStride - 1) / workStride;
+                printf("conv trace: cout %d chunks %d k %d pair %d aStages %d bStages %d x group %d resident %d, %d work items, end at %llu clk\n",
+                       p.cout, p.chunksTotal, p.k, (int)PAIR, p.aStages, p.bStages, p.bGroup, p.bResident, n, clock64() - z);
+                for (int w = 0; w < n && w < 16; ++w)
+                    printf("  item %2d: producer %6llu..%6llu | mma start %6llu tmem-free %6llu first-A %6llu issued %6llu | epilogue %6llu [t0 free %6llu math %6llu | t1 free %6llu math %6llu] %6llu\n",
+                           w, tr[0 * 16 + w] - z, tr[1 * 16 + w] - z, tr[2 * 16 + w] - z, tr[3 * 16 + w] - z,
+                           tr[4 * 16 + w] - z, tr[5 * 16 + w] - z, tr[6 * 16 + w] - z, tr[8 * 16 + w] - z, tr[9 * 16 + w] - z,
+                           tr[10 * 16 + w] - z, tr[11 * 16 + w] - z, tr[7 * 16 + w] - z);
+                for (int w = 0; w < 8; ++w)
+                    printf("  item 1, epilogue warp %d: start %6llu, tile 0 math done %6llu, tile 1 math done %6llu, past barrier %6llu\n",
+                           w + 4, tr[15 * 16 + w] - z, tr[14 * 16 + w] - z, tr[12 * 16 + w] - z, tr[13 * 16 + w] - z);
+            }
+        }
         if (PAIR)
         {
             clusterSync();      // neither CTA may exit (or free TMEM) while the other can still signal or read it
@@ -599,18 +680,22 @@ namespace opb
     // bStagesAll = weight stages of one whole Cout tile (chunks * k * k); when there is a single Cout tile and they all
     // fit next to two activation stages, the weights are loaded once per CTA and stay resident.
     template <int BN, bool PAIR>
-    static bool convSmemPlan(int k, int kxSpan, int bStagesAll, bool singleNTile, int& aStages, int& bStages,
+    static bool convSmemPlan(int k, int kxSpan, int bGroup, int bBlocksAll, bool singleNTile, int& aStages, int& bStages,
                              int& resident, int& smemBytes)
     {
         using Cfg = ConvCfg<BN>;
-        constexpr int kBStage = PAIR ? Cfg::kBBytes / 2 : Cfg::kBBytes;   // per CTA
+        const int bStage = bGroup * (PAIR ? Cfg::kBBytes / 2 : Cfg::kBBytes);   // per CTA: bGroup K blocks
+        const int bStagesAll = bBlocksAll / bGroup;
         const int aStage = 2 * convTileBytes(k, kxSpan);
-        // weight stages: as many as fit next to two activation stages, up to `want` (one weight stage is only
-        // 8 MMAs of tensor time, so the stream needs depth to cover the TMA round trip)
+        // weight stages: as many as fit next to two activation stages, up to `want` K blocks (one K block is only
+        // 8 MMAs of tensor time, so the stream needs depth to cover the TMA round trip), at least two stages
         int want = (kxSpan > 1 || BN <= 64 || PAIR) ? 6 : 4;
         if (const char* e = std::getenv("OPB200_BSTAGES"))
             want = std::atoi(e);
-        const int fitB = (kSmemLimit - (Cfg::kStagingBytes + kAuxBytes + 1024) - 2 * aStage) / kBStage;
+        want = (want + bGroup - 1) / bGroup;
+        if (want < 2)
+            want = 2;
+        const int fitB = (kSmemLimit - (Cfg::kStagingBytes + kAuxBytes + 1024) - 2 * aStage) / bStage;
         bStages = want < fitB ? want : fitB;
         if (bStages > kMaxBStages)
             bStages = kMaxBStages;
@@ -618,12 +703,12 @@ namespace opb
             return false;
         resident = 0;
         if (singleNTile && bStagesAll <= kMaxBStages &&
-            Cfg::kStagingBytes + kAuxBytes + 1024 + bStagesAll * kBStage + 2 * aStage <= kSmemLimit)
+            Cfg::kStagingBytes + kAuxBytes + 1024 + bStagesAll * bStage + 2 * aStage <= kSmemLimit)
         {
             bStages = bStagesAll;
             resident = 1;
         }
-        const int fixed = Cfg::kStagingBytes + kAuxBytes + 1024 /*alignment slack*/ + bStages * kBStage;
+        const int fixed = Cfg::kStagingBytes + kAuxBytes + 1024 /*alignment slack*/ + bStages * bStage;
         aStages = (kSmemLimit - fixed) / aStage;
         if (aStages > kMaxAStages)
             aStages = kMaxAStages;
@@ -635,12 +720,21 @@ namespace opb
     static opb200_status launchConvT(ConvParams& p, int gridCap, cudaStream_t st)
     {
         int smemBytes = 0;
-        if (!convSmemPlan<BN, PAIR>(p.k, p.kxSpan, p.chunksTotal * p.k * p.k, p.nTilesN == 1, p.aStages, p.bStages, p.bResident,
+        if (!convSmemPlan<BN, PAIR>(p.k, p.kxSpan, p.bGroup, p.chunksTotal * p.k * p.k, p.nTilesN == 1, p.aStages, p.bStages, p.bResident,
                               smemBytes))
             OPB_FAIL(OPB200_ERR_UNSUPPORTED, "conv: kernel size too large for the shared-memory pipeline");
         p.aTileBytes = convTileBytes(p.k, p.kxSpan);
         static const int debugMode = std::getenv("OPB200_CONV_DEBUG") ? std::atoi(std::getenv("OPB200_CONV_DEBUG")) : 0;
         p.debugMode = debugMode;
+        // OPB200_CONV_TRACE=chunks:cout:k[:nth] prints the role timeline of CTA 0 for the nth such launch (default 3rd)
+        if (const char* e = std::getenv("OPB200_CONV_TRACE"))
+        {
+            int tc = 0, to = 0, tk = 0, nth = 3;
+            static int seen = 0;
+            if (std::sscanf(e, "%d:%d:%d:%d", &tc, &to, &tk, &nth) >= 3 && tc == p.chunksTotal && to == p.cout && tk == p.k &&
+                ++seen == nth)
+                p.debugMode |= 4;
+        }
         static int configuredDev[64] = {0};   // attribute is per function per device; kSmemLimit covers every k
         int dev = 0;
         OPB_CUDA(cudaGetDevice(&dev));

@@ -26,5 +26,5 @@ namespace opb
     opb200_status makeFlatStoreMap(CUtensorMap* m, const void* base, int C, int W, int H, int N, int pitchW, int strideC,
                                    int boxC, int TW, int TH);
     // Weight matrix: dims (K, rows) of bf16 row-major; box (64, boxRows), SWIZZLE_128B.
-    opb200_status makeWeightMap(CUtensorMap* m, const void* base, int K, int rows, int boxRows);
+    opb200_status makeWeightMap(CUtensorMap* m, const void* base, int K, int rows, int boxRows, int boxBlocks);
 }

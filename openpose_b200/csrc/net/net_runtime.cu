@@ -65,21 +65,26 @@ namespace opb
         return OPB200_OK;
     }
 
-    opb200_status makeWeightMap(CUtensorMap* m, const void* base, int K, int rows, int boxRows)
+    // Weights [rows][K] seen as (64 K-elements, rows, K / 64 blocks): one box = boxRows x 64 elements of boxBlocks
+    // consecutive K blocks (the filter rows ky of one filter column), landing as boxBlocks swizzled (boxRows x 128 B)
+    // tiles one after the other. TMA time per box has a floor of ~0.16 us whatever its size (tests/tma_probe.cu), so
+    // one 3-block box instead of three 1-block boxes triples the weight stream's ceiling.
+    opb200_status makeWeightMap(CUtensorMap* m, const void* base, int K, int rows, int boxRows, int boxBlocks)
     {
         EncodeTiledFn fn = encodeTiled();
         if (!fn)
             OPB_FAIL(OPB200_ERR_CUDA, "cuTensorMapEncodeTiled is unavailable (driver too old?)");
-        const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
-        const cuuint64_t strides[1] = {(cuuint64_t)K * 2};
-        const cuuint32_t box[2] = {64, (cuuint32_t)boxRows};
-        const cuuint32_t es[2] = {1, 1};
-        const CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, es,
+        const cuuint64_t dims[3] = {64, (cuuint64_t)rows, (cuuint64_t)(K / 64)};
+        const cuuint64_t strides[2] = {(cuuint64_t)K * 2, 128};
+        const cuuint32_t box[3] = {64, (cuuint32_t)boxRows, (cuuint32_t)boxBlocks};
+        const cuuint32_t es[3] = {1, 1, 1};
+        const CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, es,
                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS)
         {
-            setError("cuTensorMapEncodeTiled(weights K=%d rows=%d box=%d) failed: %d", K, rows, boxRows, (int)r);
+            setError("cuTensorMapEncodeTiled(weights K=%d rows=%d box=%dx%d) failed: %d", K, rows, boxRows, boxBlocks,
+                     (int)r);
             return OPB200_ERR_CUDA;
         }
         return OPB200_OK;
@@ -871,7 +876,11 @@ namespace opb
             // OPB200_CONV_PAIR: 0 = never, 2 = every layer with BN >= 64, unset / 1 = the rule above.
             static const int pairEnv = std::getenv("OPB200_CONV_PAIR") ? std::atoi(std::getenv("OPB200_CONV_PAIR")) : 1;
             p.pairMode = (pairEnv == 2 && op.bn >= 64) || (pairEnv == 1 && op.bn >= 96 && op.k >= 3 && op.chunksTotal >= 2);
-            opb200_status st = makeWeightMap(&p.bMap, op.dW, op.kTotal, op.nTilesN * op.bn, p.pairMode ? op.bn / 2 : op.bn);
+            // weight boxes hold the k filter rows of one filter column for 3x3 layers (OPB200_CONV_BGROUP=0: one K block per box)
+            static const bool bGroupOn = !(std::getenv("OPB200_CONV_BGROUP") && std::atoi(std::getenv("OPB200_CONV_BGROUP")) == 0);
+            p.bGroup = (bGroupOn && op.k == 3) ? 3 : 1;
+            opb200_status st = makeWeightMap(&p.bMap, op.dW, op.kTotal, op.nTilesN * op.bn, p.pairMode ? op.bn / 2 : op.bn,
+                                             p.bGroup);
             if (st != OPB200_OK)
                 return st;
             p.poolFused = op.poolFused ? 1 : 0;

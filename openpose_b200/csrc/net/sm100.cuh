@@ -69,6 +69,13 @@ namespace sm100
             ::"r"(smemAddr(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smemAddr(bar)), "r"(c0), "r"(c1)
             : "memory");
     }
+    __device__ __forceinline__ void tmaLoad3d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2)
+    {
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+            ::"r"(smemAddr(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smemAddr(bar)), "r"(c0), "r"(c1), "r"(c2)
+            : "memory");
+    }
     __device__ __forceinline__ void tmaLoad4d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
                                               int c3)
     {
@@ -199,6 +206,14 @@ namespace sm100
         asm volatile(
             "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
             ::"r"(smemAddr(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(barCluster), "r"(c0), "r"(c1)
+            : "memory");
+    }
+    __device__ __forceinline__ void tmaLoad3dPair(void* dst, const CUtensorMap* m, uint32_t barCluster, int c0, int c1,
+                                                  int c2)
+    {
+        asm volatile(
+            "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+            ::"r"(smemAddr(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(barCluster), "r"(c0), "r"(c1), "r"(c2)
             : "memory");
     }
     __device__ __forceinline__ void tmaLoad4dPair(void* dst, const CUtensorMap* m, uint32_t barCluster, int c0, int c1,
