@@ -32,6 +32,7 @@ namespace opb
         int boxW;                             // box width in pixels = 8 + kxSpan - 1
         int aTileBytes;                       // boxW * (16 + k - 1) * 128, rounded up to 1024
         int aStages, bStages;                 // pipeline depths (A stage = 2 tiles x aTileBytes, B stage = BN x 128 B)
+        int stagingBufs;                      // output staging buffers: 2 = one per tile of a work item
         int bGroup;                           // K blocks (filter rows) per weight stage / TMA box: 3 for 3x3, else 1
         int bResident;                        // 1: the whole weight tile fits in the B stages and is loaded once per CTA
         const float* bias;                    // [nTilesN * BN], zero padded

@@ -108,7 +108,7 @@ namespace opb
         uint8_t* sB = sA + p.aStages * aStageBytes;                 // bStages x (BN x 128 B)
         const int bStageBytes = p.bGroup * kBStageBytes;            // one weight stage = bGroup K blocks
         uint8_t* sOut = sB + p.bStages * bStageBytes;               // staging for the TMA store
-        ConvAux* aux = reinterpret_cast<ConvAux*>(sOut + Cfg::kStagingBytes);
+        ConvAux* aux = reinterpret_cast<ConvAux*>(sOut + p.stagingBufs * Cfg::kStagingBytes);
 
         // Programmatic dependent launch: let the next layer's CTAs start their prologue on SMs this grid has
         // already vacated; they block in griddepcontrol.wait (below) until this grid has completed and flushed.
@@ -443,8 +443,15 @@ namespace opb
                     // this half's staging pieces are free once its previous TMA stores have read them
                     if (p.storeBf16 | p.poolFused)
                     {
+                        // (two staging buffers, one per tile of the item: only the stores of the tile before the previous
+                        // one must have drained -- a TMA store waits behind every load the producers have queued)
                         if (issuer)
-                            tmaStoreWaitRead0();
+                        {
+                            if (p.stagingBufs == 2)
+                                tmaStoreWaitRead1();
+                            else
+                                tmaStoreWaitRead0();
+                        }
                         namedBarrier(halfBar, 128);
                     }
                     traceStamp(traceOn && et == 0, 8 + 2 * j, wi);
@@ -535,7 +542,7 @@ namespace opb
                                 for (int i = 0; i < 16; ++i)
                                     pk[i] = 0u;
                             }
-                            const uint32_t pieceAddr = smemAddr(sOut + q * (kConvBlockM * 64));
+                            const uint32_t pieceAddr = smemAddr(sOut + (p.stagingBufs == 2 ? j * Cfg::kStagingBytes : 0) + q * (kConvBlockM * 64));
                             if (p.poolFused)
                             {
                                 // fused 2x2 / stride 2 MAX pooling (Caffe ceil mode: windows are clipped at the image
@@ -607,7 +614,7 @@ namespace opb
                             for (int q = half; q < kPieces; q += 2)
                                 if (nt * BN + q * 32 < p.cout)
                                 {
-                                    const void* src = sOut + q * (kConvBlockM * 64);
+                                    const void* src = sOut + (p.stagingBufs == 2 ? j * Cfg::kStagingBytes : 0) + q * (kConvBlockM * 64);
                                     const int c0 = nt * BN + q * 32;
                                     if (p.poolFused && p.poolOutFlat)   // per-frame map of a flat level: (c, x, n, y)
                                         tmaStore4d(&p.oMap, src, c0, sx, tc.n, sy);
@@ -681,7 +688,7 @@ namespace opb
     // fit next to two activation stages, the weights are loaded once per CTA and stay resident.
     template <int BN, bool PAIR>
     static bool convSmemPlan(int k, int kxSpan, int bGroup, int bBlocksAll, bool singleNTile, int& aStages, int& bStages,
-                             int& resident, int& smemBytes)
+                             int& resident, int& smemBytes, int stagingBufs)
     {
         using Cfg = ConvCfg<BN>;
         const int bStage = bGroup * (PAIR ? Cfg::kBBytes / 2 : Cfg::kBBytes);   // per CTA: bGroup K blocks
@@ -695,7 +702,7 @@ namespace opb
         want = (want + bGroup - 1) / bGroup;
         if (want < 2)
             want = 2;
-        const int fitB = (kSmemLimit - (Cfg::kStagingBytes + kAuxBytes + 1024) - 2 * aStage) / bStage;
+        const int fitB = (kSmemLimit - (stagingBufs * Cfg::kStagingBytes + kAuxBytes + 1024) - 2 * aStage) / bStage;
         bStages = want < fitB ? want : fitB;
         if (bStages > kMaxBStages)
             bStages = kMaxBStages;
@@ -703,12 +710,12 @@ namespace opb
             return false;
         resident = 0;
         if (singleNTile && bStagesAll <= kMaxBStages &&
-            Cfg::kStagingBytes + kAuxBytes + 1024 + bStagesAll * bStage + 2 * aStage <= kSmemLimit)
+            stagingBufs * Cfg::kStagingBytes + kAuxBytes + 1024 + bStagesAll * bStage + 2 * aStage <= kSmemLimit)
         {
             bStages = bStagesAll;
             resident = 1;
         }
-        const int fixed = Cfg::kStagingBytes + kAuxBytes + 1024 /*alignment slack*/ + bStages * bStage;
+        const int fixed = stagingBufs * Cfg::kStagingBytes + kAuxBytes + 1024 /*alignment slack*/ + bStages * bStage;
         aStages = (kSmemLimit - fixed) / aStage;
         if (aStages > kMaxAStages)
             aStages = kMaxAStages;
@@ -720,8 +727,20 @@ namespace opb
     static opb200_status launchConvT(ConvParams& p, int gridCap, cudaStream_t st)
     {
         int smemBytes = 0;
+        // two output staging buffers when they fit next to a working pipeline (OPB200_CONV_STAGING=1: always one)
+        static const int stagingEnv = std::getenv("OPB200_CONV_STAGING") ? std::atoi(std::getenv("OPB200_CONV_STAGING")) : 2;
+        p.stagingBufs = 1;
+        {
+            int a2 = 0, b2 = 0, r2 = 0, s2 = 0, a1 = 0, b1 = 0, r1 = 0, s1 = 0;
+            const bool ok1 = convSmemPlan<BN, PAIR>(p.k, p.kxSpan, p.bGroup, p.chunksTotal * p.k * p.k, p.nTilesN == 1, a1, b1, r1, s1, 1);
+            const bool ok2 = stagingEnv == 2 &&
+                             convSmemPlan<BN, PAIR>(p.k, p.kxSpan, p.bGroup, p.chunksTotal * p.k * p.k, p.nTilesN == 1, a2, b2, r2, s2, 2);
+            // not at the price of resident weights, and only with the same weight depth
+            if (ok1 && ok2 && r2 == r1 && b2 == b1)
+                p.stagingBufs = 2;
+        }
         if (!convSmemPlan<BN, PAIR>(p.k, p.kxSpan, p.bGroup, p.chunksTotal * p.k * p.k, p.nTilesN == 1, p.aStages, p.bStages, p.bResident,
-                              smemBytes))
+                              smemBytes, p.stagingBufs))
             OPB_FAIL(OPB200_ERR_UNSUPPORTED, "conv: kernel size too large for the shared-memory pipeline");
         p.aTileBytes = convTileBytes(p.k, p.kxSpan);
         static const int debugMode = std::getenv("OPB200_CONV_DEBUG") ? std::atoi(std::getenv("OPB200_CONV_DEBUG")) : 0;

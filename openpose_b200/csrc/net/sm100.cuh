@@ -103,6 +103,10 @@ namespace sm100
     {
         asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     }
+    __device__ __forceinline__ void tmaStoreWaitRead1()   // all but the most recent store group have read their source
+    {
+        asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+    }
     __device__ __forceinline__ void tmaStoreWaitAll() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
     // generic-proxy smem writes -> visible to the async proxy (TMA store reads them)
     __device__ __forceinline__ void fenceProxyAsyncShared()
