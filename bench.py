@@ -518,10 +518,19 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--traffic", type=float, default=None, help="ncu dram bytes per launch, if known")
     args = ap.parse_args()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_gpu(args)
+    try:
+        if args.impl == "reference":
+            run_reference(args)
+        else:
+            run_gpu(args)
+    finally:
+        # leave the process group cleanly: otherwise NCCL's exit warning is the last line a log shows, not the JSON line
+        try:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                dist.destroy_process_group()
+        except Exception:
+            pass
 
 
 DEFAULT_STAGES = "full"
