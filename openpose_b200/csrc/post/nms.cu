@@ -69,7 +69,10 @@ namespace opb
                && v > r2[1];
     }
 
-    // 7x7 centroid (reference: nmsBase.cpp:71-107): row-major accumulation, int->float multiply, no FMA.
+    // 7x7 centroid (reference: nmsBase.cpp:71-107): row-major accumulation, int->float multiply. CPU semantics: no
+    // FMA (x86-64 build). CUDA semantics: xAcc += x*score / yAcc += y*score are FFMAs in the reference's compiled
+    // writeResultKernel (nmsBase.cu:211-213 under nvcc's default -fmad=true), spelled out here.
+    template <int MODE>
     __device__ __forceinline__ void refinePeak(float* __restrict__ out, const float* __restrict__ s, int px, int py,
                                                int w, int h, float offx, float offy)
     {
@@ -97,8 +100,16 @@ namespace opb
             for (int dx = -3; dx <= 3; dx++)
                 if (sc[dy + 3][dx + 3] > 0)
                 {
-                    xAcc = add(xAcc, mul((float)(px + dx), sc[dy + 3][dx + 3]));
-                    yAcc = add(yAcc, mul(fy, sc[dy + 3][dx + 3]));
+                    if (MODE == OPB200_SEMANTICS_CUDA)
+                    {
+                        xAcc = __fmaf_rn((float)(px + dx), sc[dy + 3][dx + 3], xAcc);
+                        yAcc = __fmaf_rn(fy, sc[dy + 3][dx + 3], yAcc);
+                    }
+                    else
+                    {
+                        xAcc = add(xAcc, mul((float)(px + dx), sc[dy + 3][dx + 3]));
+                        yAcc = add(yAcc, mul(fy, sc[dy + 3][dx + 3]));
+                    }
                     sAcc = add(sAcc, sc[dy + 3][dx + 3]);
                 }
         }
@@ -441,7 +452,7 @@ namespace opb
                         pix = __ldcg(&a.bandLists[((size_t)ci * kNmsMaxBands + b) * a.maxPeaks + (k - slotPrefix[s][b])]);
                     }
                     const int y = pix / a.w, x = pix - y * a.w;
-                    refinePeak(a.peaks + ((size_t)ci * (a.maxPeaks + 1) + k + 1) * 3, planeOf(ci), x, y, a.w, a.h,
+                    refinePeak<MODE>(a.peaks + ((size_t)ci * (a.maxPeaks + 1) + k + 1) * 3, planeOf(ci), x, y, a.w, a.h,
                                a.offx, a.offy);
                 }
                 __syncwarp();                            // slots are reused

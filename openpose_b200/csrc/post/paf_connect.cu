@@ -77,6 +77,10 @@ namespace opb
     };
 
     // getScoreAB (CPU semantics) / process() (CUDA semantics). a, b -> (x, y, score).
+    // CUDA semantics = process() as the reference's CUDA build evaluates it: nvcc's default -fmad=true fuses
+    // norm^2 = fma(vx,vx,vy*vy), the sample position fma(lm,step,s) and the score fma(mapX,ux,mapY*uy) (SASS of
+    // pafScoreKernel<float> in oracle/_ref); spelled out with __fmaf_rn, pinned on the reference's kernel by
+    // tests/test_refcuda_gpu.py.
     template <int MODE>
     __device__ __forceinline__ float pafScore(const float* __restrict__ a, const float* __restrict__ b,
                                               const float* __restrict__ mapX, const float* __restrict__ mapY,
@@ -86,7 +90,8 @@ namespace opb
         const float vx = sub(b[0], ax), vy = sub(b[1], ay);
         const float vmax = fmaxf(fabsf(vx), fabsf(vy));
         const int n = max(5, min(25, posIntRound(sqrtf(mul(5.f, vmax)))));
-        const float norm = sqrtf(add(mul(vx, vx), mul(vy, vy)));
+        const float norm = MODE == OPB200_SEMANTICS_CUDA ? sqrtf(__fmaf_rn(vx, vx, mul(vy, vy)))
+                                                         : sqrtf(add(mul(vx, vx), mul(vy, vy)));
         if ((double)norm > 1e-6)
         {
             const float ux = divf(vx, norm), uy = divf(vy, norm);
@@ -107,15 +112,21 @@ namespace opb
             int fails = 0;
             for (int lm = 0; lm < n; lm++)
             {
-                int mx = min(c.w - 1, posIntRound(add(ax, mul((float)lm, stepx))));
-                int my = min(c.h - 1, posIntRound(add(ay, mul((float)lm, stepy))));
+                int mx, my;
                 if (MODE == OPB200_SEMANTICS_CPU)
                 {
-                    mx = max(0, mx);
-                    my = max(0, my);
+                    mx = max(0, min(c.w - 1, posIntRound(add(ax, mul((float)lm, stepx)))));
+                    my = max(0, min(c.h - 1, posIntRound(add(ay, mul((float)lm, stepy)))));
+                }
+                else
+                {
+                    mx = min(c.w - 1, posIntRound(__fmaf_rn((float)lm, stepx, ax)));
+                    my = min(c.h - 1, posIntRound(__fmaf_rn((float)lm, stepy, ay)));
                 }
                 const int idx = my * c.w + mx;
-                const float sc = add(mul(ux, __ldg(mapX + idx)), mul(uy, __ldg(mapY + idx)));
+                const float sc = MODE == OPB200_SEMANTICS_CPU
+                                     ? add(mul(ux, __ldg(mapX + idx)), mul(uy, __ldg(mapY + idx)))
+                                     : __fmaf_rn(__ldg(mapX + idx), ux, mul(__ldg(mapY + idx), uy));
                 if (sc > c.interThreshold)
                 {
                     sum = add(sum, sc);

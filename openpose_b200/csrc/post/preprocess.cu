@@ -30,17 +30,6 @@ namespace opb
         return __fmaf_rn(__uint_as_float(0x4B000000u | v), 1.f / 256.f, -32768.5f);
     }
 
-    // cubic1d of bicubic.cuh with the multiplies by +-0.5 and 2 folded into FMAs. Those products are exact (the
-    // operands here are never subnormal: taps are multiples of 2^-8 in [-0.5, 0.5) and the row results are sums of
-    // products of such values with offsets of at least 2^-13 granularity), so every rounding step is unchanged.
-    __device__ __forceinline__ float cubic1dPre(float v0, float v1, float v2, float v3, float d)
-    {
-        const float A = __fmaf_rn(0.5f, v3, sub(__fmaf_rn(-0.5f, v0, mul(1.5f, v1)), mul(1.5f, v2)));
-        const float B = __fmaf_rn(-0.5f, v3, __fmaf_rn(2.f, v2, sub(v0, mul(2.5f, v1))));
-        const float C = mul(0.5f, sub(v0, v2));
-        return cubicEval(A, B, C, v1, d);
-    }
-
     __global__ void __launch_bounds__(kPreThreads) preprocessKernel(
         float* __restrict__ dst, const unsigned char* __restrict__ src, int n, int hs, int ws, int ht, int wt,
         float scale)
@@ -99,11 +88,11 @@ namespace opb
             }
 #pragma unroll
             for (int c = 0; c < 3; c++)
-                t[c][j] = cubic1dPre(v[c][0], v[c][1], v[c][2], v[c][3], dx);
+                t[c][j] = cubic1d(v[c][0], v[c][1], v[c][2], v[c][3], dx);
         }
 #pragma unroll
         for (int c = 0; c < 3; c++)
-            o[c * plane] = cubic1dPre(t[c][0], t[c][1], t[c][2], t[c][3], dy);
+            o[c * plane] = cubic1d(t[c][0], t[c][1], t[c][2], t[c][3], dy);
     }
 
     // One thread per crop pixel. m = the 2x3 inverse map (crop pixel -> frame position), doubles as cv::Mat CV_64F.

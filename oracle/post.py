@@ -68,11 +68,11 @@ class Port:
                               C.c_float, C.c_int]
         L.opo_resize_merge.restype = None
         L.opo_resize_merge.argtypes = [_f32p, C.POINTER(_f32p), _i32p, _i32p, _f32p, _f32p, C.c_int, C.c_int,
-                                       C.c_int, C.c_int]
+                                       C.c_int, C.c_int, C.c_int]
         L.opo_maximum.restype = None
         L.opo_maximum.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int]
         L.opo_preprocess.restype = C.c_int
-        L.opo_preprocess.argtypes = [_f32p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float]
+        L.opo_preprocess.argtypes = [_f32p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int]
         L.opo_crop_warp.restype = None
         L.opo_crop_warp.argtypes = [_f32p, C.c_void_p, C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int, C.c_int]
         L.opo_heatmaps_export.restype = C.c_int
@@ -101,8 +101,10 @@ class Port:
         return peaks
 
     def resize_merge(self, srcs: Sequence[np.ndarray], ht: int, wt: int,
-                     scale_ratios: Optional[Sequence[float]] = None) -> np.ndarray:
-        """srcs[i] (C, h_i, w_i) -> (C, ht, wt); scale factors per resizeAndMergeBase.cu:379-380,475-477."""
+                     scale_ratios: Optional[Sequence[float]] = None, contract: bool = True) -> np.ndarray:
+        """srcs[i] (C, h_i, w_i) -> (C, ht, wt); scale factors per resizeAndMergeBase.cu:379-380,475-477.
+        contract: True = the FMA chain of the reference's CUDA build (pinned on the GPU against its kernels),
+        False = cuda.hu as written (pinned on the CPU against cuda.hu compiled as host C++)."""
         srcs = [np.ascontiguousarray(s, np.float32) for s in srcs]
         n = len(srcs)
         c = srcs[0].shape[0]
@@ -111,7 +113,7 @@ class Port:
         ws = np.array([s.shape[2] for s in srcs], np.int32)
         ptrs = (_f32p * n)(*[_fp(s) for s in srcs])
         dst = np.empty((c, ht, wt), np.float32)
-        self.lib.opo_resize_merge(_fp(dst), ptrs, _ip(hs), _ip(ws), _fp(sw), _fp(sh), n, c, ht, wt)
+        self.lib.opo_resize_merge(_fp(dst), ptrs, _ip(hs), _ip(ws), _fp(sw), _fp(sh), n, c, ht, wt, int(contract))
         return dst
 
     def maximum(self, heat: np.ndarray, parts: int) -> np.ndarray:
@@ -121,14 +123,14 @@ class Port:
         self.lib.opo_maximum(_fp(out), _fp(heat), parts, h, w)
         return out
 
-    def preprocess(self, frame: np.ndarray, net_size, scale: float) -> np.ndarray:
+    def preprocess(self, frame: np.ndarray, net_size, scale: float, contract: bool = True) -> np.ndarray:
         """frame (Hs,Ws,3) u8 BGR -> (3,Ht,Wt) fp32 net input; net_size = (Ht, Wt)."""
         frame = np.ascontiguousarray(frame, np.uint8)
         hs, ws, ch = frame.shape
         assert ch == 3
         out = np.empty((3, int(net_size[0]), int(net_size[1])), np.float32)
         rc = self.lib.opo_preprocess(_fp(out), frame.ctypes.data_as(C.c_void_p), hs, ws, out.shape[1],
-                                     out.shape[2], float(scale))
+                                     out.shape[2], float(scale), int(contract))
         assert rc == 0
         return out
 
@@ -336,6 +338,41 @@ class Ref:
                 with open(os.path.join(d, fn), "rb") as f:
                     out[fn] = f.read()
             return out
+
+    # ---- include/openpose_private/gpu/cuda.hu compiled as host C++ (oracle/ref_cudahu_shim.cpp) ----
+    def hu_resize8(self, src: np.ndarray, factor: int = 8) -> np.ndarray:
+        """resize8TimesKernel's pixel walk over cuda.hu's bicubicInterpolate / bicubicInterpolate8Times."""
+        src = np.ascontiguousarray(src, np.float32)
+        c, h, w = src.shape
+        out = np.empty((c, factor * h, factor * w), np.float32)
+        self.lib.refhu_resize8.restype = None
+        self.lib.refhu_resize8.argtypes = [_f32p, _f32p] + [C.c_int] * 6
+        self.lib.refhu_resize8(_fp(out), _fp(src), c, h, w, factor * h, factor * w, factor)
+        return out
+
+    def hu_resize_average(self, srcs, ht: int, wt: int, scale_ratios=None) -> np.ndarray:
+        """resizeAndAddAndAverageKernel's pixel walk over cuda.hu's bicubicInterpolate."""
+        srcs = [np.ascontiguousarray(s, np.float32) for s in srcs]
+        n, c = len(srcs), srcs[0].shape[0]
+        sw, sh = scale_factors([s.shape for s in srcs], ht, wt, scale_ratios)
+        hs = np.array([s.shape[1] for s in srcs], np.int32)
+        ws = np.array([s.shape[2] for s in srcs], np.int32)
+        ptrs = (_f32p * n)(*[_fp(s) for s in srcs])
+        out = np.empty((c, ht, wt), np.float32)
+        self.lib.refhu_resize_average.restype = None
+        self.lib.refhu_resize_average.argtypes = [_f32p, C.POINTER(_f32p), _i32p, _i32p, _f32p, _f32p] + [C.c_int] * 4
+        self.lib.refhu_resize_average(_fp(out), ptrs, _ip(hs), _ip(ws), _fp(sh), _fp(sw), n, c, ht, wt)
+        return out
+
+    def hu_resize_and_pad(self, planes: np.ndarray, net_size, scale: float) -> np.ndarray:
+        """resizeAndPadKernel's pixel walk: planes (3, Hs, Ws) fp32 -> (3, Ht, Wt)."""
+        planes = np.ascontiguousarray(planes, np.float32)
+        _, hs, ws = planes.shape
+        out = np.empty((3, int(net_size[0]), int(net_size[1])), np.float32)
+        self.lib.refhu_resize_and_pad.restype = None
+        self.lib.refhu_resize_and_pad.argtypes = [_f32p, _f32p] + [C.c_int] * 4 + [C.c_float]
+        self.lib.refhu_resize_and_pad(_fp(out), _fp(planes), hs, ws, out.shape[1], out.shape[2], float(scale))
+        return out
 
     def nms(self, heat, thr, channels, off=(0.5, 0.5), max_peaks=MAX_PEAKS, peaks=None) -> np.ndarray:
         heat = np.ascontiguousarray(heat, np.float32)

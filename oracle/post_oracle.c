@@ -9,9 +9,12 @@
  * here is pinned instead against the reference's OWN object code (oracle/_ref/libopref_post.so,
  * built from /root/reference sources) by tests/test_oracle_vs_ref.py, and against the committed
  * fixtures under tests/golden/ that were generated from that object code.
- * Exceptions ("parity unpinned", no runnable reference here): opo_resize_merge (reference = CUDA
- * device code, include/openpose_private/gpu/cuda.hu:91-144), opo_nms (mode 1), opo_pair_scores
- * (mode 1) -- CUDA-only semantics, restated from the .cu/.hu sources.
+ * The CUDA-build semantics (opo_nms / opo_pair_scores mode 1, opo_resize_merge / opo_preprocess with contract = 1)
+ * restate what the reference's CUDA kernels compute INCLUDING the FMA contraction nvcc applies to them by default
+ * (spelled with fmaf(), which is exactly fused whatever the host ISA); they are pinned on the GPU box against the
+ * reference's own kernels (oracle/_ref/libopref_cuda.so, tests/test_refcuda_gpu.py). The as-written bicubic
+ * (contract = 0) is pinned on the CPU against include/openpose_private/gpu/cuda.hu compiled as host C++
+ * (oracle/ref_cudahu_shim.cpp, tests/test_oracle_vs_ref.py).
  *
  * File references below are relative to /root/reference.
  */
@@ -20,7 +23,7 @@
 #include <string.h>
 
 #define OPO_MODE_CPU 0  /* semantics of the reference's CPU_ONLY build (the judged mode) */
-#define OPO_MODE_CUDA 1 /* semantics of the reference's CUDA kernels */
+#define OPO_MODE_CUDA 1 /* semantics of the reference's CUDA kernels as nvcc builds them (-fmad=true) */
 
 /* include/openpose/utilities/fastMath.hpp:29-32 (positiveIntRound): add 0.5 then truncate. */
 static int pos_int_round(float a) { return (int)(a + 0.5f); }
@@ -78,7 +81,9 @@ static int is_peak_cuda(const float* s, int w, int h, float thr, int x, int y)
     return 1;
 }
 
-static void refine_peak(float* out, const float* s, int px, int py, int w, int h, float offx, float offy)
+/* mode 1: nvcc fuses xAcc += x*score / yAcc += y*score of writeResultKernel (nmsBase.cu:211-213) into FFMAs
+ * (SASS of writeResultKernel<float>: two FFMA + one FADD per tap). */
+static void refine_peak(float* out, const float* s, int px, int py, int w, int h, float offx, float offy, int mode)
 {
     float xAcc = 0.f, yAcc = 0.f, sAcc = 0.f;
     for (int dy = -3; dy <= 3; dy++)
@@ -94,8 +99,16 @@ static void refine_peak(float* out, const float* s, int px, int py, int w, int h
             const float sc = s[y * w + x];
             if (sc > 0)
             {
-                xAcc += (float)x * sc;
-                yAcc += (float)y * sc;
+                if (mode == OPO_MODE_CUDA)
+                {
+                    xAcc = fmaf((float)x, sc, xAcc);
+                    yAcc = fmaf((float)y, sc, yAcc);
+                }
+                else
+                {
+                    xAcc += (float)x * sc;
+                    yAcc += (float)y * sc;
+                }
                 sAcc += sc;
             }
         }
@@ -123,7 +136,7 @@ int opo_nms(float* peaks, const float* heat, float thr, int channels, int h, int
                 if (pk)
                 {
                     count++;
-                    refine_peak(t + 3 * count, s, x, y, w, h, offx, offy);
+                    refine_peak(t + 3 * count, s, x, y, w, h, offx, offy, mode);
                 }
             }
         t[0] = (float)count;
@@ -132,20 +145,33 @@ int opo_nms(float* peaks, const float* heat, float thr, int channels, int h, int
 }
 
 /* ------------------------------------------------------------------------------------------------
- * resizeAndMerge, CUDA semantics ("parity unpinned": device code, cannot run here).
+ * resizeAndMerge, CUDA semantics.
  * include/openpose_private/gpu/cuda.hu:91-144 (index clamp, Catmull-Rom a=-0.5, evaluation order),
  * src/openpose/net/resizeAndMergeBase.cu:106-162 (x8: xs=(x+0.5)/8-0.5) and :165-196 (multi-scale:
  * xs=(x+0.5)/scaleW_i-0.5, sum in scale order, divide by count).
+ * contract = 0: cubicInterpolate as written, one rounding per operation (= cuda.hu compiled as host C++).
+ * contract = 1: the FMA chain nvcc makes of it in the reference's CUDA build (SASS of resize8TimesKernel<float>,
+ *   resizeAndAddAndAverageKernel<float>, resizeAndPadKernel<float>: A = fma(v3,.5,fma(v2,-1.5,fma(v1,1.5,v0*-.5))),
+ *   B = fma(v3,-.5,fma(v2,2,fma(v1,-2.5,v0))), t = ((A*d)*d)*d, t = fma(B*d,d,t), t = fma((v0-v2)*-.5,d,t), v1 + t).
  * ------------------------------------------------------------------------------------------------ */
-static float cubic1d(float v0, float v1, float v2, float v3, float d)
+static float cubic1d(float v0, float v1, float v2, float v3, float d, int contract)
 {
+    if (contract)
+    {
+        const float A = fmaf(v3, 0.5f, fmaf(v2, -1.5f, fmaf(v1, 1.5f, v0 * -0.5f)));
+        const float B = fmaf(v3, -0.5f, fmaf(v2, 2.f, fmaf(v1, -2.5f, v0)));
+        float t = ((A * d) * d) * d;
+        t = fmaf(B * d, d, t);
+        t = fmaf((v0 - v2) * -0.5f, d, t);
+        return v1 + t;
+    }
     return (-0.5f * v0 + 1.5f * v1 - 1.5f * v2 + 0.5f * v3) * d * d * d
            + (v0 - 2.5f * v1 + 2.f * v2 - 0.5f * v3) * d * d
            - 0.5f * (v0 - v2) * d
            + v1;
 }
 
-static float bicubic_at(const float* src, float xs, float ys, int w, int h)
+static float bicubic_at(const float* src, float xs, float ys, int w, int h, int contract)
 {
     int xi[4], yi[4];
     xi[1] = imin(w - 1, imax(0, (int)floorf(xs)));
@@ -162,15 +188,15 @@ static float bicubic_at(const float* src, float xs, float ys, int w, int h)
     for (int i = 0; i < 4; i++)
     {
         const float* r = src + (size_t)yi[i] * w;
-        t[i] = cubic1d(r[xi[0]], r[xi[1]], r[xi[2]], r[xi[3]], dx);
+        t[i] = cubic1d(r[xi[0]], r[xi[1]], r[xi[2]], r[xi[3]], dx, contract);
     }
-    return cubic1d(t[0], t[1], t[2], t[3], dy);
+    return cubic1d(t[0], t[1], t[2], t[3], dy, contract);
 }
 
 /* srcs[i]: (channels, hs[i], ws[i]); scaleW/H[i] as computed by resizeAndMergeBase.cu:379-380,475-477
  * (for one scale both are the integer ratio, e.g. 8). dst: (channels, ht, wt). */
 void opo_resize_merge(float* dst, const float* const* srcs, const int* hs, const int* ws,
-                      const float* scaleW, const float* scaleH, int nscales, int channels, int ht, int wt)
+                      const float* scaleW, const float* scaleH, int nscales, int channels, int ht, int wt, int contract)
 {
     for (int c = 0; c < channels; c++)
         for (int y = 0; y < ht; y++)
@@ -182,7 +208,7 @@ void opo_resize_merge(float* dst, const float* const* srcs, const int* hs, const
                 {
                     const float xs = ((float)x + 0.5f) / scaleW[i] - 0.5f;
                     const float ys = ((float)y + 0.5f) / scaleH[i] - 0.5f;
-                    v = bicubic_at(srcs[i] + (size_t)c * hs[i] * ws[i], xs, ys, ws[i], hs[i]);
+                    v = bicubic_at(srcs[i] + (size_t)c * hs[i] * ws[i], xs, ys, ws[i], hs[i], contract);
                     acc += v;
                 }
                 dst[((size_t)c * ht + y) * wt + x] = nscales == 1 ? v : acc / (float)nscales;
@@ -193,11 +219,11 @@ void opo_resize_merge(float* dst, const float* const* srcs, const int* hs, const
  * Frame pre-processing, the reference's device path of CvMatToOpInput::createArray
  * (src/openpose/core/cvMatToOpInput.cpp:108-148): reorderAndNormalize (src/openpose/gpu/cuda.cu:11-25)
  * into a planar float scratch, then resizeAndPadKernel (src/openpose/net/resizeAndMergeBase.cu:56-78).
- * The reference only has device code for this (nvcc may contract a*b+c there); the restatement evaluates
- * the expressions as written, without contraction (-ffp-contract=off), like the rest of this file.
+ * The reference only has device code for this; contract = 1 evaluates the bicubic as the reference's compiled kernel
+ * does (see cubic1d), contract = 0 as written. (v * (1/256) - 0.5 is exact for 8-bit v either way.)
  * src: (hs, ws, 3) u8; dst: (3, ht, wt). Returns 0, or 1 when the scratch cannot be allocated.
  * ------------------------------------------------------------------------------------------------ */
-int opo_preprocess(float* dst, const unsigned char* src, int hs, int ws, int ht, int wt, float scale)
+int opo_preprocess(float* dst, const unsigned char* src, int hs, int ws, int ht, int wt, float scale, int contract)
 {
     const size_t area = (size_t)hs * ws;
     float* planar = (float*)malloc(3 * area * sizeof(float));
@@ -215,7 +241,7 @@ int opo_preprocess(float* dst, const unsigned char* src, int hs, int ws, int ht,
                 {
                     const float xs = ((float)x + 0.5f) / scale - 0.5f;
                     const float ys = ((float)y + 0.5f) / scale - 0.5f;
-                    v = bicubic_at(planar + c * area, xs, ys, ws, hs);
+                    v = bicubic_at(planar + c * area, xs, ys, ws, hs, contract);
                 }
                 dst[((size_t)c * ht + y) * wt + x] = v;
             }
@@ -383,7 +409,9 @@ int opo_model_tables(int model, int* parts, int* pairs, const unsigned** pairTab
  * PAF line-integral score of one candidate pair.
  * mode 0: getScoreAB, src/openpose/net/bodyPartConnectorBase.cpp:12-75 (double compares, lower clamp,
  *         fall-through 0). mode 1: process(), src/openpose/net/bodyPartConnectorBase.cu:15-66 (no lower
- *         clamp, float sqrtf threshold, fall-through -1; "parity unpinned").
+ *         clamp, float sqrtf threshold, fall-through -1) with the contraction of the reference's CUDA build
+ *         (SASS of pafScoreKernel<float>: norm^2 = fma(vx,vx,vy*vy), sample = fma(lm,step,s),
+ *         score = fma(mapX,ux,mapY*uy)).
  * a, b point at (x, y, score) triplets.
  * ------------------------------------------------------------------------------------------------ */
 float opo_paf_score(const float* a, const float* b, const float* mapX, const float* mapY, int w, int h,
@@ -393,7 +421,7 @@ float opo_paf_score(const float* a, const float* b, const float* mapX, const flo
     const float vy = b[1] - a[1];
     const float vmax = fmaxf(fabsf(vx), fabsf(vy));
     const int n = imax(5, imin(25, pos_int_round(sqrtf(5 * vmax))));
-    const float norm = sqrtf(vx * vx + vy * vy);
+    const float norm = mode == OPO_MODE_CUDA ? sqrtf(fmaf(vx, vx, vy * vy)) : sqrtf(vx * vx + vy * vy);
     if ((double)norm > 1e-6)
     {
         const float sx = a[0], sy = a[1];
@@ -403,15 +431,20 @@ float opo_paf_score(const float* a, const float* b, const float* mapX, const flo
         const float stepx = vx / (float)n, stepy = vy / (float)n;
         for (int lm = 0; lm < n; lm++)
         {
-            int mx = imin(w - 1, pos_int_round(sx + (float)lm * stepx));
-            int my = imin(h - 1, pos_int_round(sy + (float)lm * stepy));
+            int mx, my;
             if (mode == OPO_MODE_CPU)
             {
-                mx = imax(0, mx);
-                my = imax(0, my);
+                mx = imax(0, imin(w - 1, pos_int_round(sx + (float)lm * stepx)));
+                my = imax(0, imin(h - 1, pos_int_round(sy + (float)lm * stepy)));
+            }
+            else
+            {
+                mx = imin(w - 1, pos_int_round(fmaf((float)lm, stepx, sx)));
+                my = imin(h - 1, pos_int_round(fmaf((float)lm, stepy, sy)));
             }
             const int idx = my * w + mx;
-            const float sc = ux * mapX[idx] + uy * mapY[idx];
+            const float sc = mode == OPO_MODE_CPU ? ux * mapX[idx] + uy * mapY[idx]
+                                                  : fmaf(mapX[idx], ux, mapY[idx] * uy);
             if (sc > interThreshold)
             {
                 sum += sc;
@@ -420,7 +453,7 @@ float opo_paf_score(const float* a, const float* b, const float* mapX, const flo
         }
         if ((float)count / (float)n > interMinAbove)
             return sum / (float)count;
-        const float l2 = sqrtf(vx * vx + vy * vy);
+        const float l2 = norm;
         if (mode == OPO_MODE_CPU)
         {
             const double thr = sqrt((double)(w * h)) / 150;

@@ -70,3 +70,65 @@ def test_planted_people_are_recovered(port):
     for p in range(6):
         d = np.abs(kp[:, :, :2][None] - planted[p, :, :2][None, None]).max(-1)  # (1, P, parts)
         assert (d.min(axis=1) < 1.0).all()
+
+
+# ---- bicubic arithmetic: the C restatement against cuda.hu itself, compiled as host C++ into oracle/_ref ----
+def _ulp_diff(a, b):
+    """max |a - b| in units of the float32 spacing at the larger magnitude of the two."""
+    return float((np.abs(a.astype(np.float64) - b) / np.spacing(np.maximum(np.abs(a), np.abs(b)).astype(np.float32)
+                                                                 + np.float32(1e-30))).max())
+
+
+@pytest.mark.parametrize("shape", [(3, 46, 82), (2, 5, 7), (2, 1, 1), (1, 23, 31)])
+def test_resize8_as_written_equals_cuda_hu(port, ref, shape):
+    """contract=False == resize8TimesKernel's walk over cuda.hu's own bicubicInterpolate / bicubicInterpolate8Times
+    (incl. its 5x5 shared tile and the first-block special case), bit for bit."""
+    rng = np.random.default_rng(1)
+    src = rng.normal(0, 1, size=shape).astype(np.float32)
+    c, h, w = shape
+    want = ref.hu_resize8(src)
+    got = port.resize_merge([src], 8 * h, 8 * w, contract=False)
+    assert np.array_equal(want, got)
+    # the CUDA build's FMA-contracted evaluation (what the GPU tests pin on the reference's kernels) stays within
+    # a few units of the last place of the output's scale
+    fused = port.resize_merge([src], 8 * h, 8 * w, contract=True)
+    scale = np.abs(src).max()
+    assert np.abs(fused - want).max() <= 8 * np.spacing(np.float32(4 * scale)), np.abs(fused - want).max()
+    assert not np.array_equal(fused, want) or h * w == 1
+
+
+def test_resize_multiscale_as_written_equals_cuda_hu(port, ref):
+    rng = np.random.default_rng(2)
+    sizes = [(46, 82), (34, 60), (22, 40), (10, 20)]
+    ratios = [1.0, 0.75, 0.5, 0.25]
+    srcs = [rng.normal(0, 1, size=(3, h, w)).astype(np.float32) for h, w in sizes]
+    want = ref.hu_resize_average(srcs, 368, 656, ratios)
+    got = port.resize_merge(srcs, 368, 656, ratios, contract=False)
+    assert np.array_equal(want, got)
+    fused = port.resize_merge(srcs, 368, 656, ratios, contract=True)
+    assert np.abs(fused - want).max() <= 8 * np.spacing(np.float32(4 * max(np.abs(s).max() for s in srcs)))
+
+
+@pytest.mark.parametrize("hs,ws,net,scale", [(20, 31, (24, 40), 1.0), (48, 64, (32, 48), 0.6), (9, 13, (16, 16), 1.2307693)])
+def test_preprocess_as_written_equals_cuda_hu(port, ref, hs, ws, net, scale):
+    rng = np.random.default_rng(hs)
+    frame = rng.integers(0, 256, size=(hs, ws, 3), dtype=np.uint8)
+    planes = frame.astype(np.float32).transpose(2, 0, 1) * np.float32(1 / 256.0) - np.float32(0.5)  # cuda.cu:23, exact
+    want = ref.hu_resize_and_pad(planes, net, scale)
+    assert np.array_equal(want, port.preprocess(frame, net, scale, contract=False))
+    assert np.abs(port.preprocess(frame, net, scale, contract=True) - want).max() <= 8 * np.spacing(np.float32(2))
+
+
+@pytest.mark.parametrize("shape", [(22, 46, 46), (4, 5, 7), (3, 33, 31)])
+def test_maximum_equals_cv_min_max_loc(port, shape):
+    """maximumCpu is cv::minMaxLoc per channel (maximumBase.cpp:28-52); cv2 is importable here."""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(3)
+    c, h, w = shape
+    src = rng.normal(0, 1, size=(c, h, w)).astype(np.float32)
+    src[0] = np.round(src[0])       # ties: both return the first maximum in raster order
+    src[1] = 0.25
+    got = port.maximum(src, c - 1)
+    for ch in range(c - 1):
+        _, vmax, _, loc = cv2.minMaxLoc(src[ch])
+        assert (got[ch, 0], got[ch, 1], got[ch, 2]) == (np.float32(loc[0]), np.float32(loc[1]), np.float32(vmax))
