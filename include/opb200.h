@@ -69,6 +69,19 @@ opb200_status opb200_nms(float* peaks, void* scratch, const float* heat, float t
                          float offset_y, const int peaks_shape[4], const int heat_shape[4], int mode,
                          void* stream);
 
+/* opb200_nms_static -- opb200_nms without a scratch argument, for callers that cannot allocate (CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc). It has NO counterpart in the reference.
+ * The scratch is a file-scope `static __device__` array of
+ * OPB200_NMS_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it until exit); the
+ * call performs no cudaMalloc / cudaFree / allocating library call. Shapes whose opb200_nms_scratch_bytes(...)
+ * exceeds the array are rejected with OPB200_ERR_INVALID (4 MiB = 5 BODY_25 or 7 COCO frames of 127 peaks).
+ * All calls share the one array per device: what must start at zero is cleared on `stream` by every call, but two
+ * calls that overlap on the GPU (different streams, no ordering between them) RACE -- serialise them.
+ * Same arguments, results and errors as opb200_nms otherwise. */
+#define OPB200_NMS_STATIC_SCRATCH_BYTES (4u << 20)
+opb200_status opb200_nms_static(float* peaks, const float* heat, float threshold, float offset_x, float offset_y,
+                                const int peaks_shape[4], const int heat_shape[4], int mode, void* stream);
+
 /* ---------------------------------------------------------------------------------------------------
  * maximum -- replaces op::maximumGpu<float> / op::maximumCpu<float>
  * (reference: include/openpose/net/maximumBase.hpp, src/openpose/net/maximumBase.cpp:8-57, maximumBase.cu:63-120).

@@ -40,6 +40,8 @@ SYMBOLS = {
     "opb200_nms_scratch_bytes": (C.c_size_t, [_I4, _I4]),
     "opb200_nms": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, _I4, _I4,
                              C.c_int, C.c_void_p]),
+    "opb200_nms_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, _I4, _I4, C.c_int,
+                                    C.c_void_p]),
     "opb200_maximum_scratch_bytes": (C.c_size_t, [_I4, _I4]),
     "opb200_maximum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, _I4, _I4, C.c_void_p]),
     "opb200_preprocess": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,

@@ -669,3 +669,51 @@ extern "C" opb200_status opb200_nms(float* peaks, void* scratch, const float* he
     OPB_LAUNCH_CHECK();
     return OPB200_OK;
 }
+
+// ----------------------------------------------------------------------------------------------------
+// opb200_nms_static: the same kernel with its scratch in a static device array, for callers that must not allocate.
+// No counterpart in the reference.
+// In host code `gNmsStaticScratch` is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+// ----------------------------------------------------------------------------------------------------
+namespace opb
+{
+    static __device__ __align__(256) unsigned char gNmsStaticScratch[OPB200_NMS_STATIC_SCRATCH_BYTES];
+}
+
+#include <mutex>
+
+extern "C" opb200_status opb200_nms_static(float* peaks, const float* heat, float threshold, float offset_x,
+                                           float offset_y, const int peaks_shape[4], const int heat_shape[4], int mode,
+                                           void* stream)
+{
+    using namespace opb;
+    OPB_REQUIRE(peaks && heat && peaks_shape && heat_shape, "nms: null argument");
+    OPB_REQUIRE(peaks_shape[0] > 0 && peaks_shape[1] > 0 && peaks_shape[2] > 1, "nms: targetSize inconsistent with sourceSize");
+    const size_t need = opb200_nms_scratch_bytes(peaks_shape, heat_shape);
+    if (need > (size_t)OPB200_NMS_STATIC_SCRATCH_BYTES)
+    {
+        setError("nms_static: these shapes need %zu bytes of scratch, the static array holds %u "
+                 "(OPB200_NMS_STATIC_SCRATCH_BYTES); use opb200_nms with a caller-owned scratch buffer",
+                 need, (unsigned)OPB200_NMS_STATIC_SCRATCH_BYTES);
+        return OPB200_ERR_INVALID;
+    }
+    static std::mutex mtx;
+    static void* devicePtr[64] = {nullptr};
+    int dev = 0;
+    OPB_CUDA(cudaGetDevice(&dev));
+    OPB_REQUIRE(dev >= 0 && dev < 64, "nms_static: device ordinal out of range");
+    void* ptr = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mtx);
+        if (devicePtr[dev] == nullptr)
+        {
+            void* p = nullptr;
+            OPB_CUDA(cudaGetSymbolAddress(&p, gNmsStaticScratch));   // address on the CURRENT device
+            devicePtr[dev] = p;
+        }
+        ptr = devicePtr[dev];
+    }
+    // opb200_nms clears the tickets (the only part that must start at zero) on `stream` and allocates nothing
+    return opb200_nms(peaks, ptr, heat, threshold, offset_x, offset_y, peaks_shape, heat_shape, mode, stream);
+}
