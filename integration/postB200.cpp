@@ -4,9 +4,15 @@
 //   op::connectBodyPartsGpu include/openpose/net/bodyPartConnectorBase.hpp:17-24 (src/.../bodyPartConnectorBase.cu:148-250)
 //   op::maximumGpu          include/openpose/net/maximumBase.hpp:14-15          (src/.../maximumBase.cu:63-120)
 // Compile this file INSTEAD of the four .cu files above. All launches go to the legacy default stream, like the
-// reference. The judged semantics is the reference's CPU_ONLY build (OPB200_SEMANTICS_CPU); define
-// OPB200_SHIM_CUDA_SEMANTICS to reproduce the CUDA build's nms borders instead.
+// reference. Which of the reference's two divergent semantics nms and the connector reproduce is chosen once per
+// process: the environment variable OPB200_SEMANTICS = "cpu" | "cuda", else the build default -- the reference's
+// CPU_ONLY build (OPB200_SEMANTICS_CPU, the judged mode), or its CUDA build when compiled with
+// -DOPB200_SHIM_CUDA_SEMANTICS (nms border rule + FMA-contracted centroid, process() scores, one global sort +
+// five-case assembly). Both are bit-exact against the reference's own object code (tests/test_post_gpu.py,
+// tests/test_refcuda_gpu.py).
 #include <opb200.h>
+#include <cstdlib>
+#include <cstring>
 #include <cuda_runtime.h>
 #include <openpose/net/bodyPartConnectorBase.hpp>
 #include <openpose/net/maximumBase.hpp>
@@ -19,11 +25,22 @@ namespace op
 {
     namespace
     {
+        int semantics()
+        {
+            static const int value = [] {
+                const char* env = std::getenv("OPB200_SEMANTICS");
+                if (env != nullptr && std::strcmp(env, "cuda") == 0)
+                    return OPB200_SEMANTICS_CUDA;
+                if (env != nullptr && std::strcmp(env, "cpu") == 0)
+                    return OPB200_SEMANTICS_CPU;
 #ifdef OPB200_SHIM_CUDA_SEMANTICS
-        const int SEMANTICS = OPB200_SEMANTICS_CUDA;
+                return OPB200_SEMANTICS_CUDA;
 #else
-        const int SEMANTICS = OPB200_SEMANTICS_CPU;
+                return OPB200_SEMANTICS_CPU;
 #endif
+            }();
+            return value;
+        }
         void check(const opb200_status status, const int line, const std::string& function, const std::string& file)
         {
             if (status != OPB200_OK)
@@ -85,11 +102,14 @@ namespace op
     {
         try
         {
-            // kernelPtr (the reference's full-size int map, nmsCaffe.cpp:123) is always large enough as scratch
-            void* scratch = kernelPtr != nullptr
-                ? static_cast<void*>(kernelPtr) : sNms.get(opb200_nms_scratch_bytes(targetSize.data(), sourceSize.data()));
+            // kernelPtr is the reference's int map of the bottom's full shape (nmsCaffe.cpp:123): reused as scratch when
+            // it is large enough (it is for every shipped net size; small maps need more than N*C*H*W ints)
+            const size_t wanted = opb200_nms_scratch_bytes(targetSize.data(), sourceSize.data());
+            const size_t kernelBytes = sizeof(int) * (size_t)sourceSize[0] * sourceSize[1] * sourceSize[2] * sourceSize[3];
+            void* scratch = (kernelPtr != nullptr && kernelBytes >= wanted)
+                ? static_cast<void*>(kernelPtr) : sNms.get(wanted);
             check(opb200_nms(targetPtr, scratch, sourcePtr, threshold, offset.x, offset.y, targetSize.data(),
-                             sourceSize.data(), SEMANTICS, nullptr), __LINE__, __FUNCTION__, __FILE__);
+                             sourceSize.data(), semantics(), nullptr), __LINE__, __FUNCTION__, __FILE__);
         }
         catch (const std::exception& e)
         {
@@ -141,7 +161,7 @@ namespace op
             params.default_nms_threshold = defaultNmsThreshold;
             params.scale_factor = scaleFactor;
             params.maximize_positives = maximizePositives ? 1 : 0;
-            params.semantics = OPB200_SEMANTICS_CPU;
+            params.semantics = semantics();
             const int parts = (int)getPoseNumberBodyParts(poseModel);
             const int channels = parts + 1 + (int)getPosePartPairs(poseModel).size();
             const int heatShape[4] = {1, channels, heatMapSize.y, heatMapSize.x};
@@ -177,7 +197,43 @@ namespace op
         }
     }
 
-    // Only float reaches these functions from the extractors; double would need a converting copy.
+    // Only float reaches these functions from the extractors. The reference's layer classes are
+    // instantiated for double too (COMPILE_TEMPLATE_FLOATING_TYPES_CLASS), so the symbols must exist: they report
+    // the missing implementation the way the reference reports a missing build option.
+    namespace
+    {
+        void doubleNotImplemented(const int line, const std::string& function)
+        {
+            error("The B200 backend implements the float instantiation only (no caller uses double).",
+                  line, function, __FILE__);
+        }
+    }
+    template <>
+    void resizeAndMergeGpu(double*, const std::vector<const double*>&, const std::array<int, 4>&,
+                           const std::vector<std::array<int, 4>>&, const std::vector<double>&)
+    {
+        doubleNotImplemented(__LINE__, __FUNCTION__);
+    }
+    template <>
+    void nmsGpu(double*, int*, const double* const, const double, const std::array<int, 4>&,
+                const std::array<int, 4>&, const Point<double>&)
+    {
+        doubleNotImplemented(__LINE__, __FUNCTION__);
+    }
+    template <>
+    void maximumGpu(double*, const double* const, const std::array<int, 4>&, const std::array<int, 4>&)
+    {
+        doubleNotImplemented(__LINE__, __FUNCTION__);
+    }
+    template <>
+    void connectBodyPartsGpu(Array<double>&, Array<double>&, const double* const, const double* const, const PoseModel,
+                             const Point<int>&, const int, const double, const double, const int, const double,
+                             const double, const double, const bool, Array<double>, double*,
+                             const unsigned int* const, const unsigned int* const, const double* const)
+    {
+        doubleNotImplemented(__LINE__, __FUNCTION__);
+    }
+
     template OP_API void resizeAndMergeGpu(
         float* targetPtr, const std::vector<const float*>& sourcePtrs, const std::array<int, 4>& targetSize,
         const std::vector<std::array<int, 4>>& sourceSizes, const std::vector<float>& scaleInputToNetInputs);
