@@ -725,8 +725,14 @@ namespace opb
     // ------------------------------------------------------------------------------------------------
     // reshape: level sizes, arena, tensor maps (reference: reshapeNetCaffe, netCaffe.cpp:105-122)
     // ------------------------------------------------------------------------------------------------
-    static opb200_status reshapeNet(Net& net, int N, int H, int W)
+    // `own` is the net's stream (created non-blocking, so the legacy default stream does not order against it): the
+    // previous shape's work on it and on the caller's stream `user` (which may still read the old output blob) is
+    // drained before the graph and the arena are torn down, and the zero fill of the new arena is enqueued on `own`,
+    // ahead of everything the following forward puts there.
+    static opb200_status reshapeNet(Net& net, int N, int H, int W, cudaStream_t own, cudaStream_t user)
     {
+        OPB_CUDA(cudaStreamSynchronize(own));
+        OPB_CUDA(cudaStreamSynchronize(user));
         if (net.graphExec)
         {
             cudaGraphExecDestroy(net.graphExec);
@@ -794,7 +800,7 @@ namespace opb
             OPB_CUDA(cudaMalloc(&net.arena, total));
             net.arenaBytes = total;
         }
-        OPB_CUDA(cudaMemset(net.arena, 0, total));
+        OPB_CUDA(cudaMemsetAsync(net.arena, 0, total, own));
         net.dInput = reinterpret_cast<float*>(net.arena + inOff);
         net.dOut32 = reinterpret_cast<float*>(net.arena + outOff);
         net.N = N;
@@ -964,7 +970,7 @@ namespace opb
         OPB_CUDA(cudaSetDevice(net.gpu));
         if (N != net.N || H != net.H || W != net.W)
         {
-            const opb200_status s = reshapeNet(net, N, H, W);
+            const opb200_status s = reshapeNet(net, N, H, W, h.own, user);
             if (s != OPB200_OK)
                 return s;
         }
@@ -986,11 +992,17 @@ namespace opb
                 OPB_CUDA(cudaStreamBeginCapture(h.own, cudaStreamCaptureModeThreadLocal));
                 s = enqueueOps(net, h.own, nullptr);
                 const cudaError_t e = cudaStreamEndCapture(h.own, &graph);
-                if (s != OPB200_OK)
-                    return s;
-                OPB_CUDA(e);
-                OPB_CUDA(cudaGraphInstantiate(&net.graphExec, graph, 0));
-                OPB_CUDA(cudaGraphDestroy(graph));
+                if (s != OPB200_OK || e != cudaSuccess)
+                {
+                    if (graph)
+                        cudaGraphDestroy(graph);   // a failed capture must not leak what it recorded
+                    if (s != OPB200_OK)
+                        return s;
+                    OPB_CUDA(e);
+                }
+                const cudaError_t ei = cudaGraphInstantiate(&net.graphExec, graph, 0);
+                cudaGraphDestroy(graph);
+                OPB_CUDA(ei);
             }
             OPB_CUDA(cudaGraphLaunch(net.graphExec, h.own));
         }

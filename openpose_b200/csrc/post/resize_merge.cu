@@ -9,8 +9,10 @@
 //     A*d*d*d + B*d*d - C*d + v1            (cuda.hu:117-120, evaluated left to right)
 // out of the 8 output rows that share the same four taps, leaving 9 FP32 operations per output pixel, so
 // the kernel is bound by the 4*C*H*W output write (HBM roofline), not by FP32 issue.
-// All arithmetic keeps the reference's operation order with contraction disabled, i.e. it is bit-identical
-// to the non-fused evaluation of cuda.hu (the oracle, oracle/post_oracle.c:opo_resize_merge).
+// All arithmetic is the reference's CUDA-build evaluation of cuda.hu -- the operation order as written with the FMA
+// contraction nvcc applies to it (bicubic.cuh) -- i.e. bit-identical to resize8TimesKernel /
+// resizeAndAddAndAverageKernel compiled from the reference (tests/test_refcuda_gpu.py) and to the oracle
+// (oracle/post_oracle.c:opo_resize_merge, contract = 1).
 #include "../common.cuh"
 #include "bicubic.cuh"
 #include <algorithm>
@@ -305,7 +307,11 @@ extern "C" opb200_status opb200_resize_merge(float* dst, const float* const* src
             OPB_CUDA(cudaMemcpyAsync(dst, srcs[0], sizeof(float) * planes * ht * wt, cudaMemcpyDeviceToDevice, st));
             return OPB200_OK;
         }
-        OPB_REQUIRE(wt / ws == 8 && ht / hs == 8,
+        // The reference admits wt / ws == 8 by INTEGER division and then runs resize8TimesKernel with
+        // rescaleFactor = ceil(ht / (float)hs) (resizeAndMergeBase.cu:352-357), which for a target that is not exactly
+        // 8x is 9 on both axes and indexes its 5x5 tile wrongly. No extractor produces such a shape
+        // (ResizeAndMergeCaffe::Reshape: exactly 8x), so it is rejected with the reference's message instead of imitated.
+        OPB_REQUIRE(wt == 8 * ws && ht == 8 * hs,
                     "Kernel only implemented for 8x resize. Notify us if this error appears.");
         const bool aligned = ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0) && (wt % 4 == 0);
         if (wt == 8 * ws && ht == 8 * hs && aligned)

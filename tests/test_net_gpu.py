@@ -17,7 +17,14 @@ from openpose_b200.net import NetB200
 from oracle import caffe_io, ref_net
 
 pytestmark = pytest.mark.gpu
-TOL_NET = 2e-2
+TOL_NET = 2e-2        # north star: absolute, heat-map-like magnitudes
+# relative bounds on the four real graphs (max-abs over ~1e6 outputs after ~50 bf16 layers; measured values are printed)
+# measured on B200 (profiles/r02_e2e_parity.txt): max-abs 4-8 % of the output RMS against the FP32 oracle AND against its
+# bf16 twin (a bf16 rounding boundary crossed in one of ~50 layers moves single outputs as much as the precision does),
+# RMS error 1.1-1.3 %. A wrong tap / channel / activation anywhere gives errors of the order of the RMS itself.
+REL_FP32 = 0.12       # max-abs vs the FP32 oracle, fraction of the output RMS
+REL_RMSE = 0.02       # RMS error vs the FP32 oracle, fraction of the output RMS
+REL_TWIN = 0.10       # max-abs vs the bf16 twin of the oracle, fraction of the output RMS
 
 
 def _layer(name, typ, bottoms, top, extra=""):
@@ -108,7 +115,18 @@ def test_openpose_models_within_tolerance(cuda, model, shape):
     net, got = _run(proto, cm, x)
     assert got.shape == want.shape == (n, protogen.OUTPUT_CHANNELS[model], h // 8, w // 8)
     err = float(np.abs(got - want).max())
-    assert err <= TOL_NET, "max-abs %.4f > %.4f (out rms %.3f)" % (err, TOL_NET, np.sqrt((want ** 2).mean()))
+    rms = float(np.sqrt((want ** 2).mean()))
+    # the bf16 twin of the oracle (bf16 weights / activations, fp32 accumulation: the product's arithmetic up to
+    # summation order) pins every layer tightly: a wrong tap, channel or activation anywhere moves it by ~rms
+    twin = ref.forward(x, keep=["net_output"], bf16_activations=True)["net_output"]
+    err16 = float(np.abs(got - twin).max())
+    rmse = float(np.sqrt(((got - want) ** 2).mean()))
+    print("%s %s: max-abs vs fp32 %.4g (%.1f%% of rms %.4g), rms error %.3g, max-abs vs bf16 twin %.4g (%.1f%% of rms)"
+          % (model, shape, err, 100 * err / rms, rms, rmse, err16, 100 * err16 / rms))
+    assert err <= TOL_NET, "max-abs %.4f > %.4f (out rms %.3f)" % (err, TOL_NET, rms)
+    assert err <= REL_FP32 * rms, (err, rms)
+    assert rmse <= REL_RMSE * rms, (rmse, rms)
+    assert err16 <= REL_TWIN * rms, (err16, rms)
     net.close()
 
 
