@@ -54,5 +54,7 @@ namespace opb
                                               //    part of the input written last by the previous layer is still in L2)
         int debugMode;                        // experiments only (OPB200_CONV_DEBUG): 1 = epilogue skips math and stores, 2 = no MMAs
         int pairMode;                         // 1: 2-CTA clusters (cta_group::2); bMap box is then (64, BN/2)
+        int tilesPerItem;                     // M tiles per CTA and work item: 2, or 1 when a small batch leaves too few tile
+                                              //   pairs to occupy the SMs (the second half of an A stage then stays unused)
     };
 }

@@ -116,7 +116,10 @@ namespace opb
         const int warp = threadIdx.x >> 5;
         const int lane = threadIdx.x & 31;
         // a work item = (group of M tiles, Cout tile); the group is a pair per CTA, i.e. a quad per CTA pair
-        const int numGroups = PAIR ? (p.numMTiles + 3) >> 2 : (p.numMTiles + 1) >> 1;
+        const int tpi = p.tilesPerItem;                             // M tiles per CTA and work item: 2, or 1 (small batches)
+        const bool two = tpi == 2;
+        const int tilesPerGroup = (PAIR ? 2 : 1) * tpi;             // a group = the tiles of one CTA, or of one CTA pair
+        const int numGroups = (p.numMTiles + tilesPerGroup - 1) / tilesPerGroup;
         const int numWork = numGroups * p.nTilesN;
         const int workStart = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
         const int workStride = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
@@ -182,7 +185,7 @@ namespace opb
             {
                 const int item = p.reverse ? numWork - 1 - work : work;
                 const int pair = PAIR ? 2 * (item / p.nTilesN) + (int)ctaRank : item / p.nTilesN;
-                const TileCoord t0 = tileCoord(p, 2 * pair), t1 = tileCoord(p, 2 * pair + 1);
+                const TileCoord t0 = tileCoord(p, tpi * pair), t1 = tileCoord(p, tpi * pair + 1);
                 const int wi = (work - workStart) / workStride;
                 traceStamp(traceOn && leader, 0, wi);
                 for (int s = 0; s < p.nSeg; ++s)
@@ -199,19 +202,21 @@ namespace opb
                                     // both CTAs' boxes are counted on the leader CTA's barrier
                                     const uint32_t bar = mapaShared(smemAddr(&aux->aFull[as]), 0);
                                     if (ctaRank == 0)
-                                        mbarExpectTx(&aux->aFull[as], 4 * boxBytes);
+                                        mbarExpectTx(&aux->aFull[as], 2u * (uint32_t)tpi * boxBytes);
                                     tmaLoad4dPair(dst, &p.aMap[s], bar, c * kConvBlockK, t0.x0 + kx - p.pad,
                                                   t0.y0 - p.pad, t0.n);
-                                    tmaLoad4dPair(dst + p.aTileBytes, &p.aMap[s], bar, c * kConvBlockK,
-                                                  t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
+                                    if (two)
+                                        tmaLoad4dPair(dst + p.aTileBytes, &p.aMap[s], bar, c * kConvBlockK,
+                                                      t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
                                 }
                                 else
                                 {
-                                    mbarExpectTx(&aux->aFull[as], 2 * boxBytes);
+                                    mbarExpectTx(&aux->aFull[as], (uint32_t)tpi * boxBytes);
                                     tmaLoad4d(dst, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
                                               t0.x0 + kx - p.pad, t0.y0 - p.pad, t0.n);
-                                    tmaLoad4d(dst + p.aTileBytes, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
-                                              t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
+                                    if (two)
+                                        tmaLoad4d(dst + p.aTileBytes, &p.aMap[s], &aux->aFull[as], c * kConvBlockK,
+                                                  t1.x0 + kx - p.pad, t1.y0 - p.pad, t1.n);
                                 }
                             }
                             __syncwarp();
@@ -331,12 +336,14 @@ namespace opb
                                             if (PAIR)
                                             {
                                                 mmaBf16Pair(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
-                                                mmaBf16Pair(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                                if (two)
+                                                    mmaBf16Pair(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
                                             }
                                             else
                                             {
                                                 mmaBf16(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
-                                                mmaBf16(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
+                                                if (two)
+                                                    mmaBf16(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
                                             }
                                         }
                                     if (groupDone && !p.bResident)   // weight slot free (in both CTAs) once these MMAs retire
@@ -434,9 +441,9 @@ namespace opb
                 traceStamp(traceOn && lane == 0 && wi == 1, 15, warp - 4);
                 bool released = false;
 #pragma unroll 1
-                for (int j = 0; j < 2; ++j)
+                for (int j = 0; j < tpi; ++j)
                 {
-                    const int mt = 2 * pair + j;
+                    const int mt = tpi * pair + j;
                     if (mt >= p.numMTiles)
                         break;                         // odd tile count: the last pair has no second tile
                     const TileCoord tc = tileCoord(p, mt);
@@ -455,6 +462,8 @@ namespace opb
                         namedBarrier(halfBar, 128);
                     }
                     traceStamp(traceOn && et == 0, 8 + 2 * j, wi);
+                    // staging buffer of this tile: one per tile of the item, or alternating between single-tile items
+                    const int sbuf = p.stagingBufs == 2 ? (two ? j : (wi & 1)) : 0;
                     const uint32_t taddr =
                         tmemBase + (acc * 2 + j) * Cfg::kAccStride + ((uint32_t)(quad * 32) << 16);
                     const int x = tc.x0 + tw, y = tc.y0 + th;
@@ -472,6 +481,7 @@ namespace opb
                         for (int i = 0; i < 8; ++i)
                             b4[i] = ldsF4(biasAddr + i * 16);
                         tmemLoadWait();
+
                         if (p.actMode == 1)            // ReLU everywhere (the VGG trunk): add + max
                         {
 #pragma unroll
@@ -542,7 +552,7 @@ namespace opb
                                 for (int i = 0; i < 16; ++i)
                                     pk[i] = 0u;
                             }
-                            const uint32_t pieceAddr = smemAddr(sOut + (p.stagingBufs == 2 ? j * Cfg::kStagingBytes : 0) + q * (kConvBlockM * 64));
+                            const uint32_t pieceAddr = smemAddr(sOut + sbuf * Cfg::kStagingBytes + q * (kConvBlockM * 64));
                             if (p.poolFused)
                             {
                                 // fused 2x2 / stride 2 MAX pooling (Caffe ceil mode: windows are clipped at the image
@@ -590,7 +600,7 @@ namespace opb
                     }
                     traceStamp(traceOn && et == 0, 9 + 2 * j, wi);
                     traceStamp(traceOn && lane == 0 && wi == 1, j ? 12 : 14, warp - 4);
-                    if (j == 1 || mt + 1 >= p.numMTiles)
+                    if (j == tpi - 1 || mt + 1 >= p.numMTiles)
                     {
                         // all TMEM reads of this thread are complete (wait::ld above): hand both accumulators back NOW,
                         // before the stores -- a TMA store queues behind every load the producer has in flight
@@ -614,7 +624,7 @@ namespace opb
                             for (int q = half; q < kPieces; q += 2)
                                 if (nt * BN + q * 32 < p.cout)
                                 {
-                                    const void* src = sOut + (p.stagingBufs == 2 ? j * Cfg::kStagingBytes : 0) + q * (kConvBlockM * 64);
+                                    const void* src = sOut + sbuf * Cfg::kStagingBytes + q * (kConvBlockM * 64);
                                     const int c0 = nt * BN + q * 32;
                                     if (p.poolFused && p.poolOutFlat)   // per-frame map of a flat level: (c, x, n, y)
                                         tmaStore4d(&p.oMap, src, c0, sx, tc.n, sy);
@@ -688,7 +698,7 @@ namespace opb
     // fit next to two activation stages, the weights are loaded once per CTA and stay resident.
     template <int BN, bool PAIR>
     static bool convSmemPlan(int k, int kxSpan, int bGroup, int bBlocksAll, bool singleNTile, int& aStages, int& bStages,
-                             int& resident, int& smemBytes, int stagingBufs)
+                             int& resident, int& smemBytes, int stagingBufs, bool deepB = false)
     {
         using Cfg = ConvCfg<BN>;
         const int bStage = bGroup * (PAIR ? Cfg::kBBytes / 2 : Cfg::kBBytes);   // per CTA: bGroup K blocks
@@ -702,6 +712,10 @@ namespace opb
         want = (want + bGroup - 1) / bGroup;
         if (want < 2)
             want = 2;
+        // small-batch launches (one single-tile work item per CTA): the MMA phase is a chain of weight-box round trips
+        // (timeline: 146 clk per MMA with 2 stages in flight), so the ring takes the whole Cout tile if it fits
+        if (deepB && bStagesAll > want)
+            want = bStagesAll;
         const int fitB = (kSmemLimit - (stagingBufs * Cfg::kStagingBytes + kAuxBytes + 1024) - 2 * aStage) / bStage;
         bStages = want < fitB ? want : fitB;
         if (bStages > kMaxBStages)
@@ -727,20 +741,21 @@ namespace opb
     static opb200_status launchConvT(ConvParams& p, int gridCap, cudaStream_t st)
     {
         int smemBytes = 0;
+        const bool deepB = p.tilesPerItem == 1;
         // two output staging buffers when they fit next to a working pipeline (OPB200_CONV_STAGING=1: always one)
         static const int stagingEnv = std::getenv("OPB200_CONV_STAGING") ? std::atoi(std::getenv("OPB200_CONV_STAGING")) : 2;
         p.stagingBufs = 1;
         {
             int a2 = 0, b2 = 0, r2 = 0, s2 = 0, a1 = 0, b1 = 0, r1 = 0, s1 = 0;
-            const bool ok1 = convSmemPlan<BN, PAIR>(p.k, p.kxSpan, p.bGroup, p.chunksTotal * p.k * p.k, p.nTilesN == 1, a1, b1, r1, s1, 1);
+            const bool ok1 = convSmemPlan<BN, PAIR>(p.k, p.kxSpan, p.bGroup, p.chunksTotal * p.k * p.k, p.nTilesN == 1, a1, b1, r1, s1, 1, deepB);
             const bool ok2 = stagingEnv == 2 &&
-                             convSmemPlan<BN, PAIR>(p.k, p.kxSpan, p.bGroup, p.chunksTotal * p.k * p.k, p.nTilesN == 1, a2, b2, r2, s2, 2);
+                             convSmemPlan<BN, PAIR>(p.k, p.kxSpan, p.bGroup, p.chunksTotal * p.k * p.k, p.nTilesN == 1, a2, b2, r2, s2, 2, deepB);
             // not at the price of resident weights, and only with the same weight depth
             if (ok1 && ok2 && r2 == r1 && b2 == b1)
                 p.stagingBufs = 2;
         }
         if (!convSmemPlan<BN, PAIR>(p.k, p.kxSpan, p.bGroup, p.chunksTotal * p.k * p.k, p.nTilesN == 1, p.aStages, p.bStages, p.bResident,
-                              smemBytes, p.stagingBufs))
+                              smemBytes, p.stagingBufs, deepB))
             OPB_FAIL(OPB200_ERR_UNSUPPORTED, "conv: kernel size too large for the shared-memory pipeline");
         p.aTileBytes = convTileBytes(p.k, p.kxSpan);
         static const int debugMode = std::getenv("OPB200_CONV_DEBUG") ? std::atoi(std::getenv("OPB200_CONV_DEBUG")) : 0;
@@ -764,7 +779,10 @@ namespace opb
             configuredDev[dev & 63] = 1;
         }
         // one CTA per pair of M tiles; in pair mode one 2-CTA cluster per quad
-        const int numWork = (PAIR ? (p.numMTiles + 3) / 4 : (p.numMTiles + 1) / 2) * p.nTilesN;
+        if (p.tilesPerItem != 1)
+            p.tilesPerItem = 2;
+        const int tilesPerGroup = (PAIR ? 2 : 1) * p.tilesPerItem;
+        const int numWork = (p.numMTiles + tilesPerGroup - 1) / tilesPerGroup * p.nTilesN;
         int grid = PAIR ? 2 * (numWork < gridCap / 2 ? numWork : gridCap / 2) : (numWork < gridCap ? numWork : gridCap);
         if (grid < (PAIR ? 2 : 1))
             grid = PAIR ? 2 : 1;

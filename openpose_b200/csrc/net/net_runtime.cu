@@ -67,7 +67,7 @@ namespace opb
 
     // Weights [rows][K] seen as (64 K-elements, rows, K / 64 blocks): one box = boxRows x 64 elements of boxBlocks
     // consecutive K blocks (the filter rows ky of one filter column), landing as boxBlocks swizzled (boxRows x 128 B)
-    // tiles one after the other. TMA time per box has a floor of ~0.16 us whatever its size (tests/tma_probe.cu), so
+    // tiles one after the other. TMA time per box has a floor of ~0.16 us whatever its size (tools/tma_probe.cu), so
     // one 3-block box instead of three 1-block boxes triples the weight stream's ceiling.
     opb200_status makeWeightMap(CUtensorMap* m, const void* base, int K, int rows, int boxRows, int boxBlocks)
     {
@@ -148,6 +148,7 @@ namespace opb
         View out;
         // conv
         int cin = 0, cout = 0, k = 1, pad = 0, bn = 128, nTilesN = 1, chunksTotal = 0, kTotal = 0;
+        int bnEff = 128;                    // Cout tile of the current shape: bn, or a divisor of it at small batches (reshapeNet)
         int segChunks[kConvMaxSegments] = {0, 0, 0, 0};
         std::vector<__nv_bfloat16> hostW;   // [nTilesN*bn][kTotal]
         std::vector<float> hostBias, hostSlope;
@@ -845,7 +846,45 @@ namespace opb
             p.boxW = kConvTileW + p.kxSpan - 1;
             p.nSeg = (int)op.in.size();
             p.chunksTotal = op.chunksTotal;
-            p.nTilesN = op.nTilesN;
+            // Small batches: a 46x82 level has 33 M tiles per frame, i.e. 17 tile pairs (9 quads in pair mode) for 148 SMs.
+            // When the default tiling leaves most SMs idle, work items shrink -- to ONE M tile per CTA, then to narrower
+            // Cout tiles (a divisor of the weight layout's tile, so weights / bias tables are shared) -- until about three
+            // quarters of the SMs have one. CTA pairs stay where they pay: a cta_group::2 MMA (M = 256) retires in the time a
+            // cta_group::1 MMA (M = 128) needs (timeline of a 128->128 layer at batch 1: 64 against 171 clk per MMA).
+            // OPB200_CONV_SMALL=0 disables.
+            static const bool smallOn = !(std::getenv("OPB200_CONV_SMALL") && std::atoi(std::getenv("OPB200_CONV_SMALL")) == 0);
+            static const int minBn = std::getenv("OPB200_CONV_SMALL_MINBN") ? std::atoi(std::getenv("OPB200_CONV_SMALL_MINBN")) : 32;
+            op.bnEff = op.bn;
+            p.tilesPerItem = 2;
+            int smallPair = -1;   // -1: the default pair rule decides
+            {
+                const int wantCtas = (kNumSMsB200 * 3) / 4;
+                const bool pairShape = op.k >= 3 && op.chunksTotal >= 2;
+                auto ctas = [&](int bn, int tpi, bool pair) {
+                    const int perGroup = (pair ? 2 : 1) * tpi;
+                    return (long long)((p.numMTiles + perGroup - 1) / perGroup) * ((op.cout + bn - 1) / bn) * (pair ? 2 : 1);
+                };
+                const bool defaultPair = op.bn >= 96 && pairShape;
+                if (smallOn && ctas(op.bn, 2, defaultPair) < wantCtas)
+                {
+                    p.tilesPerItem = 1;
+                    const int cands[3] = {op.bn, op.bn == 128 ? 64 : 32, 32};
+                    for (int ci = 0; ci < 3; ++ci)
+                    {
+                        if (op.bn % cands[ci] != 0 || cands[ci] > op.bnEff || cands[ci] < minBn)
+                            continue;
+                        if (pairShape && op.bn >= 64 && cands[ci] < 64)
+                            continue;   // rather 68 CTAs issuing pair MMAs than 132 issuing single-CTA ones
+                        op.bnEff = cands[ci];
+                        smallPair = (pairShape && op.bnEff >= 64) ? 1 : 0;
+                        if (ctas(op.bnEff, 1, smallPair == 1) >= wantCtas)
+                            break;
+                    }
+                    if (smallPair < 0)
+                        smallPair = defaultPair ? 1 : 0;
+                }
+            }
+            p.nTilesN = (op.cout + op.bnEff - 1) / op.bnEff;
             p.cout = op.cout;
             p.bias = op.dBias;
             p.slope = op.dSlope;
@@ -882,10 +921,12 @@ namespace opb
             // OPB200_CONV_PAIR: 0 = never, 2 = every layer with BN >= 64, unset / 1 = the rule above.
             static const int pairEnv = std::getenv("OPB200_CONV_PAIR") ? std::atoi(std::getenv("OPB200_CONV_PAIR")) : 1;
             p.pairMode = (pairEnv == 2 && op.bn >= 64) || (pairEnv == 1 && op.bn >= 96 && op.k >= 3 && op.chunksTotal >= 2);
+            if (smallPair >= 0 && pairEnv != 0)
+                p.pairMode = smallPair;
             // weight boxes hold the k filter rows of one filter column for 3x3 layers (OPB200_CONV_BGROUP=0: one K block per box)
             static const bool bGroupOn = !(std::getenv("OPB200_CONV_BGROUP") && std::atoi(std::getenv("OPB200_CONV_BGROUP")) == 0);
             p.bGroup = (bGroupOn && op.k == 3) ? 3 : 1;
-            opb200_status st = makeWeightMap(&p.bMap, op.dW, op.kTotal, op.nTilesN * op.bn, p.pairMode ? op.bn / 2 : op.bn,
+            opb200_status st = makeWeightMap(&p.bMap, op.dW, op.kTotal, op.nTilesN * op.bn, p.pairMode ? op.bnEff / 2 : op.bnEff,
                                              p.bGroup);
             if (st != OPB200_OK)
                 return st;
@@ -934,7 +975,7 @@ namespace opb
                 s = launchInputPatch(viewPtr(op.out), net.dInput, net.N, op.inC, h, w, op.k, op.pad,
                                      net.buffers[op.out.buf].C, st);
                 break;
-            case OP_CONV: s = launchConv(op.cp, op.bn, net.gridCap, st); break;
+            case OP_CONV: s = launchConv(op.cp, op.bnEff, net.gridCap, st); break;
             case OP_FIRSTCONV:
                 s = launchFirstConv(viewPtr(op.out), net.dInput, reinterpret_cast<const uint32_t*>(op.dW), op.dBias,
                                     op.dSlope, net.N, op.inC, h, w, op.k, op.pad, op.cout, net.buffers[op.out.buf].C,

@@ -1,5 +1,5 @@
 """Supplementary measurement: net-forward throughput of the four OpenPose graphs (BASELINE.json configs 1 and 3) with
-seeded random-init weights. usage: PYTHONPATH=. python tests/bench_models.py [steps]"""
+seeded random-init weights. usage: PYTHONPATH=. python tools/bench_models.py [steps]"""
 import json
 import sys
 import torch

@@ -1,5 +1,5 @@
 """Experiment: post-processing of step i (HBM bound) on a second stream while the net of step i+1 (tensor bound)
-runs. usage: PYTHONPATH=. python tests/bench_pipeline.py [batch] [steps] [net_priority] [post_priority]"""
+runs. usage: PYTHONPATH=. python tools/bench_pipeline.py [batch] [steps] [net_priority] [post_priority]"""
 import sys
 import torch
 import bench

@@ -1,7 +1,7 @@
 // Research tool (GPU): what bounds the L2 -> shared-memory operand stream of the conv kernel?
 // Persistent CTAs (one per SM) issue TMA box loads from an NHWC bf16 activation tensor (or a weight matrix) through a
 // ring of D shared-memory stages and nothing else; reports bytes/clk/SM and TB/s for box shape x depth x channel pitch.
-//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o openpose_b200/lib/tma_probe tests/tma_probe.cu
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o openpose_b200/lib/tma_probe tools/tma_probe.cu
 #include "../openpose_b200/csrc/net/sm100.cuh"
 #include <cstdio>
 #include <cstdlib>
