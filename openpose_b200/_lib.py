@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libopb200.so")
+# OPB200_LIB_PATH: A/B runs of two builds of the SAME product library on one box (tools/ab_libs.sh); never a fallback
+LIB_PATH = os.environ.get("OPB200_LIB_PATH") or os.path.join(_HERE, "lib", "libopb200.so")
 
 OK = 0
 SEMANTICS_CPU, SEMANTICS_CUDA = 0, 1

@@ -113,7 +113,8 @@ namespace opb
         // Programmatic dependent launch: let the next layer's CTAs start their prologue on SMs this grid has
         // already vacated; they block in griddepcontrol.wait (below) until this grid has completed and flushed.
         asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-        const int warp = threadIdx.x >> 5;
+        const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // warp-uniform FOR THE COMPILER: role branches
+                                                                                  // become uniform branches, loop state may live in uniform registers
         const int lane = threadIdx.x & 31;
         // a work item = (group of M tiles, Cout tile); the group is a pair per CTA, i.e. a quad per CTA pair
         const int tpi = p.tilesPerItem;                             // M tiles per CTA and work item: 2, or 1 (small batches)
@@ -312,62 +313,46 @@ namespace opb
                         // once per stage and advanced by adding 16-byte units to the start-address field.
                         const uint64_t aBase0 = smemDescSw128(smemAddr(sA + as * aStageBytes), groupPitch);
                         const uint64_t aBase1 = aBase0 + (uint64_t)(p.aTileBytes >> 4);
-                        uint32_t first = ax != 0;
+                        // one weight box = bGroup filter rows of one filter column: wait for it, issue all its MMAs in one
+                        // statement (sm100.cuh: mmaGroupBf16), hand the slot back
+                        uint32_t accFirst = ax != 0;
                         for (int kxi = 0; kxi < p.kxSpan; ++kxi)
                         {
                             uint64_t aDesc0 = aBase0 + (uint64_t)(kxi * 8);
                             uint64_t aDesc1 = aBase1 + (uint64_t)(kxi * 8);
-                            int kyInGroup = 0;
-                            for (int ky = 0; ky < p.k; ++ky)
+                            for (int ky = 0; ky < p.k; ky += p.bGroup)
                             {
-                                if (kyInGroup == 0)
+                                mbarWait(&aux->bFull[bs], bPhase);
+                                tcFenceAfter();
+                                const uint64_t bDesc = bBase + (uint64_t)(bs * p.bGroup * (kBStageBytes >> 4));
+                                if (leader && !(p.debugMode & 2))
                                 {
-                                    mbarWait(&aux->bFull[bs], bPhase);
-                                    tcFenceAfter();
+                                    if (p.bGroup == 3)
+                                        mmaGroupBf16<3, PAIR>(tmemD0, tmemD1, aDesc0, aDesc1, bDesc, (uint32_t)kyStep,
+                                                              (uint32_t)(kBStageBytes >> 4), idesc, accFirst, (uint32_t)steps,
+                                                              two ? 1u : 0u);
+                                    else
+                                        mmaGroupBf16<1, PAIR>(tmemD0, tmemD1, aDesc0, aDesc1, bDesc, (uint32_t)kyStep,
+                                                              (uint32_t)(kBStageBytes >> 4), idesc, accFirst, (uint32_t)steps,
+                                                              two ? 1u : 0u);
                                 }
-                                const uint64_t bDesc = bBase + (uint64_t)((bs * p.bGroup + kyInGroup) * (kBStageBytes >> 4));
-                                const bool groupDone = ++kyInGroup == p.bGroup;
-                                if (leader)
+                                if (leader && !p.bResident)   // weight slot free (in both CTAs) once these MMAs retire
                                 {
-#pragma unroll
-                                    for (int kk = 0; kk < kConvBlockK / 16; ++kk)   // 16 bf16 = 32 bytes per MMA along K
-                                        if (kk < steps && !(p.debugMode & 2))
-                                        {
-                                            if (PAIR)
-                                            {
-                                                mmaBf16Pair(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
-                                                if (two)
-                                                    mmaBf16Pair(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
-                                            }
-                                            else
-                                            {
-                                                mmaBf16(tmemD0, aDesc0 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
-                                                if (two)
-                                                    mmaBf16(tmemD1, aDesc1 + 2 * kk, bDesc + 2 * kk, idesc, first | kk);
-                                            }
-                                        }
-                                    if (groupDone && !p.bResident)   // weight slot free (in both CTAs) once these MMAs retire
-                                    {
-                                        if (PAIR)
-                                            mmaCommitPair(&aux->bEmpty[bs]);
-                                        else
-                                            mmaCommit(&aux->bEmpty[bs]);
-                                    }
+                                    if (PAIR)
+                                        mmaCommitPair(&aux->bEmpty[bs]);
+                                    else
+                                        mmaCommit(&aux->bEmpty[bs]);
                                 }
                                 __syncwarp();
-                                first = 1;
+                                accFirst = 1;
                                 // resident weights: the slots are never recycled, their (only) phase stays complete
-                                if (groupDone)
+                                if (++bs == p.bStages)
                                 {
-                                    kyInGroup = 0;
-                                    if (++bs == p.bStages)
-                                    {
-                                        bs = 0;
-                                        bPhase ^= p.bResident ? 0u : 1u;
-                                    }
+                                    bs = 0;
+                                    bPhase ^= p.bResident ? 0u : 1u;
                                 }
-                                aDesc0 += kyStep;
-                                aDesc1 += kyStep;
+                                aDesc0 += kyStep * (uint64_t)p.bGroup;
+                                aDesc1 += kyStep * (uint64_t)p.bGroup;
                             }
                         }
                         if (leader)                               // activation slot free

@@ -264,6 +264,74 @@ namespace sm100
             : "memory");
     }
 
+    // ---------------------------------------------------------------- grouped MMA issue
+    // All MMAs of one weight box (G filter rows x 4 k-steps x 1..2 M tiles) in ONE asm statement. Written in C++ the issue
+    // loop recomputes every descriptor in vector registers and moves it to the uniform datapath with R2UR before each
+    // UTCHMMA (~30 R2UR and ~100 instructions per filter row): ~600 cycles per filter row whatever the MMA shape, which
+    // paced every layer whose 8 MMAs per row need less tensor time than that (N <= 96, single-tile items). Here the
+    // operands cross to uniform registers once per box and the per-MMA descriptors are uniform adds.
+    //   d0, d1: TMEM accumulators of the two M tiles (d1 only used when two != 0)
+    //   a0, a1: smem descriptors of the two tiles at the box's first filter row; aRowStep = one filter row down (16-byte units)
+    //   b: smem descriptor of the box's first K block; bRowStep = one K block further (16-byte units)
+    //   accFirst: 0 = the very first MMA of the work item overwrites the accumulator; steps: 16-channel k-steps (1..4)
+    // Only the low word of a descriptor changes between MMAs (start address, bits [0,14)); the adds are 32-bit and the
+    // 64-bit operand is the register pair {low, constant high word}.
+#define OPB_MMA_ROW(CG, ACC0)                                                                        \
+    "mov.b64 da, {ra0, ah};\n\tmov.b64 db, {rb, bh};\n\tmov.b64 dc, {ra1, ah};\n\t"                  \
+    "tcgen05.mma.cta_group::" CG ".kind::f16 [%0], da, db, %7, " ACC0 ";\n\t"                        \
+    "@pt tcgen05.mma.cta_group::" CG ".kind::f16 [%1], dc, db, %7, " ACC0 ";\n\t"                    \
+    "add.u32 ta, ra0, 2;\n\tadd.u32 tb, rb, 2;\n\tadd.u32 tc, ra1, 2;\n\t"                         \
+    "mov.b64 da, {ta, ah};\n\tmov.b64 db, {tb, bh};\n\tmov.b64 dc, {tc, ah};\n\t"                    \
+    "@p1 tcgen05.mma.cta_group::" CG ".kind::f16 [%0], da, db, %7, pT;\n\t"                          \
+    "@p1t tcgen05.mma.cta_group::" CG ".kind::f16 [%1], dc, db, %7, pT;\n\t"                         \
+    "add.u32 ta, ra0, 4;\n\tadd.u32 tb, rb, 4;\n\tadd.u32 tc, ra1, 4;\n\t"                         \
+    "mov.b64 da, {ta, ah};\n\tmov.b64 db, {tb, bh};\n\tmov.b64 dc, {tc, ah};\n\t"                    \
+    "@p2 tcgen05.mma.cta_group::" CG ".kind::f16 [%0], da, db, %7, pT;\n\t"                          \
+    "@p2t tcgen05.mma.cta_group::" CG ".kind::f16 [%1], dc, db, %7, pT;\n\t"                         \
+    "add.u32 ta, ra0, 6;\n\tadd.u32 tb, rb, 6;\n\tadd.u32 tc, ra1, 6;\n\t"                         \
+    "mov.b64 da, {ta, ah};\n\tmov.b64 db, {tb, bh};\n\tmov.b64 dc, {tc, ah};\n\t"                    \
+    "@p3 tcgen05.mma.cta_group::" CG ".kind::f16 [%0], da, db, %7, pT;\n\t"                          \
+    "@p3t tcgen05.mma.cta_group::" CG ".kind::f16 [%1], dc, db, %7, pT;\n\t"
+#define OPB_MMA_NEXT_ROW "add.u32 ra0, ra0, %5;\n\tadd.u32 ra1, ra1, %5;\n\tadd.u32 rb, rb, %6;\n\t"
+#define OPB_MMA_PROLOGUE                                                                             \
+    "{\n\t.reg .pred pf, pT, pt, p1, p2, p3, p1t, p2t, p3t;\n\t"                                     \
+    ".reg .b32 ra0, ra1, rb, ah, bh, ta, tb, tc;\n\t.reg .b64 da, db, dc;\n\t"                       \
+    "setp.ne.u32 pf, %8, 0;\n\tsetp.eq.u32 pT, 0, 0;\n\tsetp.ne.u32 pt, %10, 0;\n\t"                 \
+    "setp.gt.u32 p1, %9, 1;\n\tsetp.gt.u32 p2, %9, 2;\n\tsetp.gt.u32 p3, %9, 3;\n\t"                 \
+    "and.pred p1t, p1, pt;\n\tand.pred p2t, p2, pt;\n\tand.pred p3t, p3, pt;\n\t"                    \
+    "mov.b64 {ra0, ah}, %2;\n\tmov.b64 {ra1, tc}, %3;\n\tmov.b64 {rb, bh}, %4;\n\t"
+#define OPB_MMA_OPERANDS                                                                             \
+    ::"r"(d0), "r"(d1), "l"(a0), "l"(a1), "l"(b), "r"(aRowStep), "r"(bRowStep), "r"(idesc), "r"(accFirst), "r"(steps), \
+      "r"(two)                                                                                       \
+    : "memory"
+    template <int G, bool PAIR>
+    __device__ __forceinline__ void mmaGroupBf16(uint32_t d0, uint32_t d1, uint64_t a0, uint64_t a1, uint64_t b,
+                                                 uint32_t aRowStep, uint32_t bRowStep, uint32_t idesc, uint32_t accFirst,
+                                                 uint32_t steps, uint32_t two)
+    {
+        static_assert(G == 1 || G == 3, "a weight box holds one filter row or the three rows of a 3x3 filter column");
+        if (PAIR)
+        {
+            if (G == 1)
+                asm volatile(OPB_MMA_PROLOGUE OPB_MMA_ROW("2", "pf") "}" OPB_MMA_OPERANDS);
+            else
+                asm volatile(OPB_MMA_PROLOGUE OPB_MMA_ROW("2", "pf") OPB_MMA_NEXT_ROW OPB_MMA_ROW("2", "pT") OPB_MMA_NEXT_ROW
+                                 OPB_MMA_ROW("2", "pT") "}" OPB_MMA_OPERANDS);
+        }
+        else
+        {
+            if (G == 1)
+                asm volatile(OPB_MMA_PROLOGUE OPB_MMA_ROW("1", "pf") "}" OPB_MMA_OPERANDS);
+            else
+                asm volatile(OPB_MMA_PROLOGUE OPB_MMA_ROW("1", "pf") OPB_MMA_NEXT_ROW OPB_MMA_ROW("1", "pT") OPB_MMA_NEXT_ROW
+                                 OPB_MMA_ROW("1", "pT") "}" OPB_MMA_OPERANDS);
+        }
+    }
+#undef OPB_MMA_ROW
+#undef OPB_MMA_NEXT_ROW
+#undef OPB_MMA_PROLOGUE
+#undef OPB_MMA_OPERANDS
+
     // ---------------------------------------------------------------- epilogue helpers
     __device__ __forceinline__ float4 ldsF4(uint32_t saddr)
     {
