@@ -230,6 +230,11 @@ void opb200_net_destroy(opb200_net* net);
 opb200_status opb200_net_forward(opb200_net* net, const float* input, int input_on_device, const int shape[4],
                                  void* stream);
 opb200_status opb200_net_output(opb200_net* net, const float** dev_ptr, int shape[4]);
+/* The net's own fp32 NCHW input buffer for `shape` (re-plans buffers when the shape changes, like a forward): a producer
+ * on the device (opb200_preprocess, opb200_crop_warp) writes the input there on `stream` and passes the same pointer to
+ * opb200_net_forward(..., input_on_device = 1, ...), which then skips its input copy. No reference counterpart (Caffe's
+ * input blob is written through mutable_gpu_data, netCaffe.cpp:230-236). */
+opb200_status opb200_net_input_buffer(opb200_net* net, const int shape[4], float** dev_ptr, void* stream);
 opb200_status opb200_net_info(opb200_net* net, opb200_net_info_t* info);
 /* Test hook: any intermediate blob as fp32 NCHW on the host (host_nchw NULL = shape query). Synchronises. */
 opb200_status opb200_net_read_blob(opb200_net* net, const char* name, float* host_nchw, size_t capacity,
@@ -281,6 +286,45 @@ opb200_status opb200_coco_json_record(opb200_coco_json* handle, const float* key
                                       int people, int parts, const char* image_name,
                                       unsigned long long frame_number);
 opb200_status opb200_coco_json_close(opb200_coco_json* handle);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Multi-GPU body-pose engine: u8 BGR frames in, people out, frame order kept -- the hot path of the reference's
+ * worker topology (one PoseExtractor per GPU on its own thread fed round-robin, results re-ordered by frame id:
+ * include/openpose/wrapper/wrapperAuxiliary.hpp:181-219,326-338, include/openpose/thread/wQueueOrderer.hpp:12-80) and
+ * of the per-frame chain CvMatToOpInput (device branch) -> PoseExtractorCaffe::forwardPass.
+ * One host thread + compute stream + copy stream per device, `lanes` batches in flight per device, batches dealt to
+ * the devices round-robin, no cross-device exchange. Per batch: H2D of the u8 frames, opb200_preprocess into the net's
+ * input buffer, opb200_net_forward, opb200_resize_merge, opb200_nms, opb200_connect, D2H of the results.
+ *   acquire -> pinned host staging buffer of batch * frame_h * frame_w * 3 bytes to write frames into (blocks while every
+ *              lane of the next device is busy); commit(first_frame_id, n) -> enqueue its first n frames;
+ *   submit  = acquire + memcpy + commit;
+ *   next    -> the oldest submitted batch not yet returned (blocks until it is finished): keypoints (n, capacity, parts,
+ *              3), scores (n, capacity), counts (n) into HOST buffers of at least `batch` frames.
+ * acquire / commit / submit from one producer thread, next from one consumer thread (they may be the same).
+ * ------------------------------------------------------------------------------------------------- */
+typedef struct opb200_engine opb200_engine;
+typedef struct opb200_engine_config
+{
+    int pose_model;                 /* OPB200_POSE_* */
+    int net_w, net_h;               /* net input resolution, multiples of 8 (656 x 368) */
+    int frame_w, frame_h;           /* producer resolution of the u8 BGR frames */
+    int batch;                      /* frames per batch (per device) */
+    int lanes;                      /* batches in flight per device, 1..8 (2 overlaps H2D with compute) */
+    int capacity;                   /* people kept per frame */
+    float scale_input_to_net;       /* ScaleAndSizeExtractor::extract's scaleInputToNetInputs[0] */
+    float nms_threshold;            /* PoseProperty::NMSThreshold */
+    opb200_connect_params connect;  /* incl. scale_factor = scaleNetToOutput and semantics (also used by nms) */
+} opb200_engine_config;
+opb200_status opb200_engine_create(opb200_engine** out, const char* prototxt, const char* caffemodel,
+                                   const int* gpu_ids, int n_gpus, const opb200_engine_config* cfg);
+void opb200_engine_destroy(opb200_engine* engine);
+opb200_status opb200_engine_acquire(opb200_engine* engine, unsigned char** staging);
+opb200_status opb200_engine_commit(opb200_engine* engine, unsigned long long first_frame_id, int n_frames);
+opb200_status opb200_engine_submit(opb200_engine* engine, unsigned long long first_frame_id,
+                                   const unsigned char* frames, int n_frames);
+opb200_status opb200_engine_next(opb200_engine* engine, unsigned long long* first_frame_id, int* n_frames,
+                                 float* keypoints, float* scores, int* counts);
+int opb200_engine_in_flight(opb200_engine* engine);   /* batches submitted and not yet returned by next */
 
 #ifdef __cplusplus
 }

@@ -636,7 +636,7 @@ namespace opb
                 }
             }
             if (issuer)
-                tmaStoreWaitAll();
+                tmaStoreWaitAll();   // (waiting only for the stores' smem reads was measured: no gain, so the stronger wait stays)
         }
         tcFenceBefore();
         if (traceOn)

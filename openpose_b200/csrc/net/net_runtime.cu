@@ -1018,8 +1018,9 @@ namespace opb
         // fork from the caller's stream onto the net's own (capturable) stream
         OPB_CUDA(cudaEventRecord(h.evIn, user));
         OPB_CUDA(cudaStreamWaitEvent(h.own, h.evIn, 0));
-        OPB_CUDA(cudaMemcpyAsync(net.dInput, input, net.inputBytes,
-                                 onDevice ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, h.own));
+        if (input != net.dInput)   // (opb200_net_input_buffer: the caller wrote the input in place)
+            OPB_CUDA(cudaMemcpyAsync(net.dInput, input, net.inputBytes,
+                                     onDevice ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, h.own));
         if (net.useGraph)
         {
             if (!net.graphExec)
@@ -1145,6 +1146,30 @@ extern "C" void opb200_net_destroy(opb200_net* n)
     if (n->h.evOut)
         cudaEventDestroy(n->h.evOut);
     delete n;
+}
+
+extern "C" opb200_status opb200_net_input_buffer(opb200_net* n, const int shape[4], float** dev_ptr, void* stream)
+{
+    OPB_REQUIRE(n && shape && dev_ptr, "net_input_buffer: null argument");
+    Net& net = n->h.net;
+    if (shape[0] <= 0 || shape[2] <= 0 || shape[3] <= 0)
+    {
+        setError("The Array inputData cannot be empty.");
+        return OPB200_ERR_INVALID;
+    }
+    OPB_REQUIRE(shape[1] == net.inputC, "The Array inputData must have 4 dimensions: [batch size, 3 (RGB), height, width].");
+    OPB_CUDA(cudaSetDevice(net.gpu));
+    if (shape[0] != net.N || shape[2] != net.H || shape[3] != net.W)
+    {
+        const opb200_status s = reshapeNet(net, shape[0], shape[2], shape[3], n->h.own, static_cast<cudaStream_t>(stream));
+        if (s != OPB200_OK)
+            return s;
+        // the zero fill of a fresh arena runs on the net's stream: the caller's writes on `stream` come after it
+        OPB_CUDA(cudaEventRecord(n->h.evOut, n->h.own));
+        OPB_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), n->h.evOut, 0));
+    }
+    *dev_ptr = net.dInput;
+    return OPB200_OK;
 }
 
 extern "C" opb200_status opb200_net_forward(opb200_net* n, const float* input, int input_on_device,

@@ -30,6 +30,7 @@ _lib.register({
     "opb200_net_destroy": (None, [C.c_void_p]),
     "opb200_net_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, _lib._I4, C.c_void_p]),
     "opb200_net_output": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), _lib._I4]),
+    "opb200_net_input_buffer": (C.c_int, [C.c_void_p, _lib._I4, C.POINTER(C.c_void_p), C.c_void_p]),
     "opb200_net_info": (C.c_int, [C.c_void_p, C.POINTER(NetInfo)]),
     "opb200_net_read_blob": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_size_t, _lib._I4]),
     "opb200_net_describe": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]),

@@ -31,6 +31,7 @@ def test_library_exports_every_declared_symbol():
 def test_python_binding_covers_header():
     import openpose_b200.net  # noqa: F401  (registers its symbols)
     import openpose_b200.filestream  # noqa: F401
+    import openpose_b200.engine  # noqa: F401
     declared = _declared_symbols()
     assert declared <= set(_lib.SYMBOLS), sorted(declared - set(_lib.SYMBOLS))
     L = _lib.lib()
