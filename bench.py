@@ -3,9 +3,16 @@
 
 A "step" = one batch of B synthetic frames through the hot path on every rank:
   [net forward (NetB200, bf16 tcgen05 convs)] -> resizeAndMerge x8 -> nms -> bodyPartConnector
-`value`     : frames/s with the step's inputs already resident in HBM (CUDA events, max over ranks).
-`e2e`       : the same through the public host-buffer call: pinned host input -> H2D -> path -> D2H of
-              keypoints/scores/counts, copies inside the timed region.
+`value`     : frames/s with the step's inputs already resident in HBM (CUDA events, max over ranks). A random-init net
+              emits noise (no trained weights offline), so by default the post-processing of the step runs on planted
+              8-person net outputs of the same shape while the net runs on the frames (--post-input net: on the net's own
+              output); rank 0 checks the people it assembles against the reference's CPU code (`parity_check`).
+`e2e`       : frames/s through the library's frame-level API (opb200_engine_*): u8 BGR 1280x720 frames in pinned host
+              memory -> H2D -> device pre-processing -> net -> resize -> nms -> connector (on the net's own output) -> D2H
+              of keypoints/scores/counts, every copy inside the timed region, two batches in flight.
+`ref_gpu_ms`: the reference's OWN CUDA kernels (oracle/_ref/libopref_cuda.so) for the post-processing stages on one frame
+              of the same inputs, same box: the GPU-vs-GPU baseline next to `stages_ms`.
+`latency`   : one frame (batch 1) through the same path, device-resident input.
 `roofline`  : the dominant kernel of the step (conv family when the net is on the path: tensor bound;
               resizeAndMerge otherwise: hbm bound), timed live with CUDA events on the launching stream.
 `cpu_baseline` / `--impl reference`: the reference's CPU code for the path on the host cores
@@ -30,6 +37,7 @@ if ROOT not in sys.path:
 import numpy as np  # noqa: E402
 
 NET_H, NET_W = 368, 656          # BODY_25 net resolution 656x368 (BASELINE.json metric)
+FRAME_H, FRAME_W = 720, 1280     # producer resolution of the end-to-end leg (BASELINE.json configs[0])
 OUT_H, OUT_W = NET_H // 8, NET_W // 8
 PARTS, CHANNELS = 25, 78
 MAXP = 127
@@ -139,7 +147,9 @@ class PostPath:
         self.sc = torch.empty((batch, capacity), device=device)
         self.cnt = torch.empty((batch,), dtype=torch.int32, device=device)
         self.capacity = capacity
-        self.launches_per_step = None
+        # kernels + memsets per step: resize 1, nms (ticket memset + kernel) 2, connector (memset + candidates + match +
+        # assemble) 4 -- csrc/post/{resize_merge,nms,paf_connect}.cu
+        self.launches_per_step = 7
 
     def run(self, net_out, ev=None):
         """net_out: (B,78,46,82) device tensor. ev: optional list collecting (name, start, end) events."""
@@ -187,9 +197,9 @@ def cpu_reference_post(net_out: np.ndarray):
     t1b = time.perf_counter()
     peaks = impl.nms(heat, 0.05, PARTS, off=(NMS_OFFSET, NMS_OFFSET))
     t2 = time.perf_counter()
-    kp = impl.connect(heat, peaks, 0, scale=SCALE_NET_TO_OUTPUT)[0]
+    kp, sc = impl.connect(heat, peaks, 0, scale=SCALE_NET_TO_OUTPUT)[:2]
     t3 = time.perf_counter()
-    return dict(resize_ms=(t1 - t0) * 1e3, nms_ms=(t2 - t1b) * 1e3, connect_ms=(t3 - t2) * 1e3,
+    return dict(keypoints=kp, scores=sc, resize_ms=(t1 - t0) * 1e3, nms_ms=(t2 - t1b) * 1e3, connect_ms=(t3 - t2) * 1e3,
                 total_s=(t1 - t0) + (t3 - t1b), resize_impl=resize_impl, people=int(kp.shape[0]), kind="reference" if use_ref else "port")
 
 
@@ -258,6 +268,7 @@ def run_gpu(args):
     B = args.batch
     have_net = False
     net = None
+    launches_net = 0
     if args.stages in ("full", "net"):
         from openpose_b200 import net as netmod
         net = netmod.bench_net(B, NET_H, NET_W, dev)      # NetB200 with seeded random-init BODY_25 weights
@@ -265,9 +276,13 @@ def run_gpu(args):
     post = PostPath(B, dev) if args.stages in ("full", "post") else None
 
     # synthetic inputs (per rank, different seeds: weak scaling, fixed per-GPU work)
+    planted_dev = None
     if have_net:
         from openpose_b200 import synth
         host_in = torch.from_numpy(synth.frames_to_net_input(synth.frames(B, NET_H, NET_W, 100 + rank)))
+        if post is not None and args.post_input == "planted":
+            planted_host = planted_net_outputs(B, args.people, 1000 * (rank + 1))
+            planted_dev = torch.from_numpy(planted_host).to(dev)
     else:
         host_in = torch.from_numpy(planted_net_outputs(B, args.people, 1000 * (rank + 1)))
     host_in = host_in.pin_memory()
@@ -281,7 +296,7 @@ def run_gpu(args):
         if have_net:
             x = net.forward_device(x, ev)
         if post is not None:
-            return post.run(x, ev)
+            return post.run(planted_dev if planted_dev is not None else x, ev)
         return x
 
     def step_host():
@@ -322,63 +337,79 @@ def run_gpu(args):
     frames_all = sum_over_ranks(float(B * args.steps), world, dev)
     value = frames_all / (ms_total * 1e-3)
 
+    if have_net:
+        launches_net = net.launches_per_step() + 1        # + the input copy node
     stage_ms = {}
     for name, a, b in stage_events:
         stage_ms.setdefault(name, []).append(a.elapsed_time(b))
     stage_avg = {k: float(np.mean(v)) for k, v in stage_ms.items()}
 
     # ---- timed region 2: end to end through host buffers -------------------------------------------
-    # Full path: the host input of step i+1 is copied H2D on a copy stream into the second of two device buffers
-    # while step i computes (what a caller that wants throughput does around the public API). Every step still
-    # copies its inputs H2D from pinned memory and its results D2H inside the timed region.
-    lanes = None
-    if have_net and post is not None and not args.no_e2e_overlap:
-        copy_stream = torch.cuda.Stream(device=dev)
-        lanes = [{"dev": torch.empty_like(dev_in), "h2d": torch.cuda.Event(), "done": torch.cuda.Event(),
-                  "kp": torch.empty((B, 256, PARTS, 3)).pin_memory(), "sc": torch.empty((B, 256)).pin_memory(),
-                  "cnt": torch.empty((B,), dtype=torch.int32).pin_memory()} for _ in range(2)]
-
-        def issue_h2d(i):
-            ln = lanes[i % 2]
-            with torch.cuda.stream(copy_stream):
-                copy_stream.wait_event(ln["done"])   # the step that last read this buffer has finished
-                ln["dev"].copy_(host_in, non_blocking=True)
-                ln["h2d"].record()
-
-        def run_steps(n):
-            cur = torch.cuda.current_stream()
-            issue_h2d(0)
-            for i in range(n):
-                ln = lanes[i % 2]
-                if i + 1 < n:
-                    issue_h2d(i + 1)
-                cur.wait_event(ln["h2d"])
-                out = post.run(net.forward_device(ln["dev"]))
-                ln["kp"].copy_(out[0], non_blocking=True)
-                ln["sc"].copy_(out[1], non_blocking=True)
-                ln["cnt"].copy_(out[2], non_blocking=True)
-                ln["done"].record()
-                if i >= 1:
-                    lanes[(i - 1) % 2]["done"].synchronize()   # the host consumes step i-1's people
-            lanes[(n - 1) % 2]["done"].synchronize()
+    parity = None
+    if post is not None and planted_dev is not None and rank == 0:
+        parity = (post.kp[0].cpu().numpy(), post.sc[0].cpu().numpy(), int(post.cnt[0].item()), planted_host[0])
+    engine_mode = have_net and post is not None and not args.no_engine
+    if engine_mode:
+        # The library's frame-level API: u8 frames in pinned staging -> people, two batches in flight per device. The
+        # staging buffers are filled once (the frames stay in pinned host memory); every timed step copies its batch H2D
+        # and its results D2H. Steady state: each iteration takes the oldest batch and submits the next.
+        from openpose_b200 import modelgen, synth
+        from openpose_b200.engine import PoseEngine
+        net.net.close()            # the engine owns its own net; free this one's arena first
+        del dev_in
+        torch.cuda.empty_cache()
+        proto, cm, _, _ = modelgen.build_files("body_25", 1234)
+        eng = PoseEngine(proto, cm, gpus=[local], net_size=(NET_W, NET_H), frame_size=(FRAME_W, FRAME_H), batch=B,
+                         lanes=2, capacity=256)
+        frames = synth.frames(B, FRAME_H, FRAME_W, 300 + rank)
+        fid = 0
+        for _ in range(2):                       # fill both lanes' staging buffers
+            eng.acquire()[:] = frames
+            eng.commit(fid, B)
+            fid += B
+        for _ in range(3):                       # warm-up in steady state
+            eng.next(copy=False)
+            eng.acquire()
+            eng.commit(fid, B)
+            fid += B
+        barrier(world)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            eng.next(copy=False)
+            eng.acquire()
+            eng.commit(fid, B)
+            fid += B
+        wall = time.perf_counter() - t0
+        last_id = -1
+        while eng.in_flight():
+            last_id, kp_e, _, cnt_e = eng.next(copy=False)
+        assert last_id == fid - B and kp_e.shape[0] == B and cnt_e.shape[0] == B, "engine lost a batch"
+        barrier(world)
+        eng.close()
+        ms_e2e = max_over_ranks(wall * 1e3, world, dev)
+        h2d = B * FRAME_H * FRAME_W * 3
+        d2h = B * (256 * PARTS * 3 + 256 + 1) * 4
+        e2e_mode = ("opb200_engine_*: u8 BGR %dx%d frames in pinned host staging -> H2D -> device pre-processing -> net -> "
+                    "resize -> nms -> connector (on the net's own output) -> D2H; 2 batches in flight; host wall clock over "
+                    "%d steady-state steps" % (FRAME_W, FRAME_H, args.steps))
     else:
-        def run_steps(n):
-            for _ in range(n):
-                step_host()
-    run_steps(3)
-    barrier(world)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    e0.record()
-    run_steps(args.steps)
-    e1.record()
-    torch.cuda.synchronize()
-    wall = time.perf_counter() - t0
-    barrier(world)
-    ms_e2e = max_over_ranks(max(e0.elapsed_time(e1), wall * 1e3), world, dev)
+        run_steps = lambda n: [step_host() for _ in range(n)]   # noqa: E731
+        run_steps(3)
+        barrier(world)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        e0.record()
+        run_steps(args.steps)
+        e1.record()
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        barrier(world)
+        ms_e2e = max_over_ranks(max(e0.elapsed_time(e1), wall * 1e3), world, dev)
+        h2d = host_in.numel() * host_in.element_size()
+        d2h = (h_kp.numel() + h_sc.numel() + h_cnt.numel()) * 4 if post is not None else net.output_bytes()
+        e2e_mode = "one call per step through the Python mirror of the operator API, every step synchronous"
     e2e_value = frames_all / (ms_e2e * 1e-3)
-    h2d = host_in.numel() * host_in.element_size()
-    d2h = (h_kp.numel() + h_sc.numel() + h_cnt.numel()) * 4 if post is not None else net.output_bytes()
 
     if rank != 0:
         return
@@ -386,10 +417,13 @@ def run_gpu(args):
     if have_net:
         conv_ms = stage_avg["net_convs"]
         achieved = CONV_GFLOP_PER_FRAME * B / conv_ms          # GFLOP/ms = TFLOP/s
-        roof = {"bound": "tensor", "kernel": "conv_igemm_tcgen05 (all conv launches of one step)",
+        roof = {"bound": "tensor", "kernel": "whole net forward of one step: input copy + first conv + 113 conv_igemm_tcgen05 launches",
                 "achieved": achieved, "peak": peaks_tbl["tf_sustained"], "unit": "TFLOP/s",
-                "frac": achieved / peaks_tbl["tf_sustained"], "traffic": conv_traffic(B),
-                "peak_source": peaks_tbl["source"] + " sustained bf16", "launch_ms": conv_ms}
+                "frac": achieved / peaks_tbl["tf_sustained"], "frac_of_burst_peak": achieved / peaks_tbl["tf_burst"],
+                "traffic": conv_traffic(B), "traffic_source": "committed ncu capture profiles/r01_conv_traffic.json "
+                "(not measured in this run)" if conv_traffic(B) is not None else None,
+                "peak_source": peaks_tbl["source"] + " sustained bf16 (burst %.0f)" % peaks_tbl["tf_burst"],
+                "launch_ms": conv_ms}
     else:
         rms = stage_avg["resize"]
         achieved = RESIZE_BYTES * B / (rms * 1e-3) / 1e9
@@ -404,9 +438,19 @@ def run_gpu(args):
     # ---- CPU baseline (rank 0, N=1 only): bounded sample = 1 frame of the same workload ----------
     cpu = None
     if world == 1 and not args.no_cpu:
-        cpu = cpu_baseline(args, host_in)
+        cpu = cpu_baseline(args, host_in, parity[3] if parity is not None else None)
+    parity_check = None
+    if parity is not None and cpu is not None and "_keypoints" in cpu:
+        kp_cpu, sc_cpu = cpu.pop("_keypoints"), cpu.pop("_scores")
+        n = parity[2]
+        parity_check = {"frame": 0, "people_gpu": n, "people_cpu": int(kp_cpu.shape[0]),
+                        "keypoints_bit_equal": bool(n == kp_cpu.shape[0] and np.array_equal(parity[0][:n], kp_cpu)
+                                                    and np.array_equal(parity[1][:n], sc_cpu))}
+        assert parity_check["people_gpu"] == parity_check["people_cpu"] > 0 and parity_check["keypoints_bit_equal"], parity_check
+    ref_gpu = reference_gpu_stages(parity[3], dev) if (parity is not None and world == 1 and not args.no_cpu) else None
+    latency = measure_latency(args, dev) if (have_net and post is not None and world == 1 and not args.no_latency) else None
 
-    launches = (net.launches_per_step() if have_net else 0) + (5 if post is not None else 0)
+    launches = (launches_net if have_net else 0) + (post.launches_per_step if post is not None else 0)
     line = {
         "metric": "BODY_25 656x368 frames/s", "value": value, "unit": "frames/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,
@@ -414,7 +458,9 @@ def run_gpu(args):
         "dtype": "bf16 (convs, fp32 accumulate) + f32 (post-processing)" if have_net else "f32",
         "data": "synthetic",
         "config": {"workload": ("BODY_25 net 656x368, scale_number 1, batch of %d synthetic frames per GPU, "
-                                "random-init caffemodel; stages=%s" % (B, args.stages)) if have_net else
+                                "random-init caffemodel; stages=%s; post-processing input: %s" % (
+                                    B, args.stages, ("planted %d-person net outputs (78x46x82)" % args.people)
+                                    if planted_dev is not None else "the net's own output")) if have_net else
                                ("BODY_25 post-processing only (net not on the path yet): %d planted %d-person "
                                 "net outputs (78x46x82) per GPU -> resizeAndMerge x8 -> nms -> connector"
                                 % (B, args.people)),
@@ -423,23 +469,91 @@ def run_gpu(args):
                          % (B * CHANNELS * NET_H * NET_W * 4 // 2 ** 20),
                    "sharding": "frame-sharded, no collective"},
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": ms_e2e / args.steps,
-                "mode": ("input of step i+1 copied H2D on a copy stream while step i computes (two device input "
-                         "buffers); every step copies its inputs H2D from pinned memory and its results D2H")
-                        if lanes is not None else
-                        "one engine instance, every step synchronous"},
+                "ms_per_step": ms_e2e / args.steps, "mode": e2e_mode},
         "gpu_launches": launches * args.steps,
         "roofline": roof, "stages_ms": stages, "clocks": clocks,
     }
     if cpu is not None:
         line["cpu_baseline"] = cpu
+    if parity_check is not None:
+        line["parity_check"] = parity_check
+    if ref_gpu is not None:
+        line["ref_gpu_ms"] = ref_gpu
+    if latency is not None:
+        line["latency"] = latency
     print(json.dumps(line))
+
+
+def reference_gpu_stages(net_out: np.ndarray, dev, reps: int = 5):
+    """The reference's own CUDA kernels (oracle/_ref/libopref_cuda.so, compiled unmodified from /root/reference) on ONE
+    frame of the step's post-processing input: ms per frame and stage, CUDA events on the legacy default stream they launch
+    on (connectBodyPartsGpu's host half -- D2H of the score cube, sort, assembly -- by host clock). None when the library
+    was not built."""
+    import torch
+    from oracle.ref_cuda import RefCuda, REFCUDA_SO
+    if not os.path.exists(REFCUDA_SO):
+        return None
+    rc = RefCuda()
+    src = torch.from_numpy(np.ascontiguousarray(net_out[None])).to(dev)
+    heat = torch.empty((1, CHANNELS, NET_H, NET_W), device=dev)
+    peaks = torch.zeros((1, PARTS, MAXP + 1, 3), device=dev)
+    kernel = torch.empty(heat.numel() + 16 * (NET_W + 16), dtype=torch.int32, device=dev)
+    cube = torch.empty((26, MAXP, MAXP), device=dev)
+    t = {"resize": [], "nms": [], "connect": []}
+    people = 0
+    for r in range(reps + 1):
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        torch.cuda.synchronize()
+        ev[0].record()
+        rc.resize_merge(heat, [src])
+        ev[1].record()
+        rc.nms(peaks, heat, 0.05, (NMS_OFFSET, NMS_OFFSET), kernel=kernel)
+        ev[2].record()
+        torch.cuda.synchronize()
+        h0 = time.perf_counter()
+        kp, _, _ = rc.connect(heat[0], peaks[0], 0, scale=SCALE_NET_TO_OUTPUT, cube_dev=cube, want_cube=False)
+        torch.cuda.synchronize()
+        h1 = time.perf_counter()
+        people = int(kp.shape[0])
+        if r:   # first repetition = warm-up
+            t["resize"].append(ev[0].elapsed_time(ev[1]))
+            t["nms"].append(ev[1].elapsed_time(ev[2]))
+            t["connect"].append((h1 - h0) * 1e3)
+    return {"per": "frame", "resize": round(float(np.median(t["resize"])), 4), "nms": round(float(np.median(t["nms"])), 4),
+            "connect": round(float(np.median(t["connect"])), 4), "people": people,
+            "what": "resizeAndMergeGpu, nmsGpu, connectBodyPartsGpu of the reference (CUDA-build semantics) on frame 0"}
+
+
+def measure_latency(args, dev, steps: int = 100):
+    """One frame at a time (batch 1) through net -> resize -> nms -> connector, device-resident input."""
+    import torch
+    from openpose_b200 import net as netmod
+    from openpose_b200 import synth
+    net1 = netmod.bench_net(1, NET_H, NET_W, dev)
+    post1 = PostPath(1, dev)
+    x = torch.from_numpy(synth.frames_to_net_input(synth.frames(1, NET_H, NET_W, 7))).to(dev)
+    planted = torch.from_numpy(planted_net_outputs(1, args.people, 77)).to(dev) if args.post_input == "planted" else None
+    for _ in range(10):
+        out = net1.forward_device(x)
+        post1.run(planted if planted is not None else out)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        out = net1.forward_device(x)
+        post1.run(planted if planted is not None else out)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    net1.net.close()
+    return {"batch": 1, "ms_per_frame": round(ms, 4), "frames_per_s": round(1e3 / ms, 1), "steps": steps,
+            "what": "device-resident input, frames issued back to back on one stream"}
 
 
 # ----------------------------------------------------------------------------------------------------
 # CPU baseline + reference arm (host cores; the reference's CPU code where it compiled, see oracle/)
 # ----------------------------------------------------------------------------------------------------
-def cpu_baseline(args, host_in):
+def cpu_baseline(args, host_in, post_input=None):
     """One frame of the same workload on the host cores. Post: single thread (the reference has no
     OpenMP in src/openpose/net). Net (when on the path): torch-CPU FP32 restatement of Caffe, all cores."""
     cores = os.cpu_count() or 1
@@ -454,7 +568,8 @@ def cpu_baseline(args, host_in):
     else:
         net_out = host_in[:1].numpy()
     if args.stages in ("full", "post"):
-        r = cpu_reference_post(np.ascontiguousarray(net_out[0]))
+        # the post-processing input of the GPU arm: planted net outputs (default) or the net's own output
+        r = cpu_reference_post(np.ascontiguousarray(post_input if post_input is not None else net_out[0]))
         # "reference" only when every timed stage is the reference's own object code; with the net on the
         # path 95 % of the time is the torch-CPU restatement of Caffe, so the line as a whole is a port
         kind = r["kind"] if args.stages == "post" else "port"
@@ -464,7 +579,11 @@ def cpu_baseline(args, host_in):
                       "connect_ms": round(r["connect_ms"], 2), "people": r["people"],
                       "resize_impl": r["resize_impl"]})
         total += r["total_s"]
-    return {"value": 1.0 / total, "unit": "frames/s", "cores": cores if args.stages != "post" else 1,
+        out_kp, out_sc = r["keypoints"], r["scores"]
+    else:
+        out_kp = out_sc = None
+    extra = {"_keypoints": out_kp, "_scores": out_sc} if (out_kp is not None and post_input is not None) else {}
+    return {**extra, "value": 1.0 / total, "unit": "frames/s", "cores": cores if args.stages != "post" else 1,
             "kind": kind, "sample": "1 frame of the step's batch (frame 0), all stages once", "stages": parts}
 
 
@@ -484,12 +603,15 @@ def run_reference(args):
     steps = max(1, min(args.steps, 3))
     warm = 1 if args.warmup > 0 else 0
     last = None
+    post_in = planted_net_outputs(1, args.people, 1000)[0] if (args.stages == "full" and args.post_input == "planted") else None
     for _ in range(warm):
-        last = cpu_baseline(args, host_in)
+        last = cpu_baseline(args, host_in, post_in)
     dt = 0.0   # sum of the timed stage regions (excludes the oracle's own bookkeeping between stages)
     for _ in range(steps):
-        last = cpu_baseline(args, host_in)
+        last = cpu_baseline(args, host_in, post_in)
         dt += 1.0 / last["value"]
+    for k in ("_keypoints", "_scores"):
+        last.pop(k, None)
     v = steps * B / dt
     line = {"impl": "reference", "metric": "BODY_25 656x368 frames/s", "value": v, "unit": "frames/s",
             "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": steps, "warmup": warm,
@@ -506,15 +628,19 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=100)   # 1.2 s per timed region: the sustained (power-capped) rate
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=44,
                     help="frames per step per GPU (44 x 33 tiles of the 46x82 layers = 4.9 waves of 148 SMs x 2 tiles)")
     ap.add_argument("--people", type=int, default=8, help="planted people per frame (post-only workload)")
     ap.add_argument("--stages", default=DEFAULT_STAGES, choices=["full", "post", "net"])
-    ap.add_argument("--no-e2e-overlap", action="store_true",
-                    help="end-to-end region with one engine instance, every step fully synchronous")
+    ap.add_argument("--post-input", default="planted", choices=["planted", "net"],
+                    help="what the post-processing of a full step runs on: planted --people-person net outputs (default; a "
+                         "random-init net emits noise that assembles nobody) or the net's own output")
+    ap.add_argument("--no-engine", action="store_true",
+                    help="end-to-end region through the Python mirror of the operator API instead of opb200_engine_*")
+    ap.add_argument("--no-latency", action="store_true", help="skip the batch-1 latency leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--traffic", type=float, default=None, help="ncu dram bytes per launch, if known")
     args = ap.parse_args()
