@@ -151,3 +151,52 @@ def test_random_init_is_seeded_and_caffemodel_roundtrips(tmp_path):
     assert set(back) == set(a)
     assert all(np.array_equal(x, y) for k in a for x, y in zip(a[k], back[k]))
     assert sum(x.size for k in a for x in a[k]) > 26_000_000          # BODY_25: 26.15 M parameters
+
+
+# ---- the net oracle's convolution / pooling arithmetic against the reference's bundled Caffe code ----
+def _ref_caffe():
+    import ctypes
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libopref_caffe.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libopref_caffe.so not built (needs /root/reference at build time)")
+    L = ctypes.CDLL(path)
+    fp = ctypes.POINTER(ctypes.c_float)
+    L.refcaffe_conv.argtypes = [fp, fp, fp, fp] + [ctypes.c_int] * 6
+    L.refcaffe_conv.restype = None
+    L.refcaffe_max_pool.argtypes = [fp, fp] + [ctypes.c_int] * 6
+    L.refcaffe_max_pool.restype = ctypes.c_int
+    return L, fp
+
+
+@pytest.mark.parametrize("cin,cout,h,w,k", [(3, 8, 9, 11, 3), (16, 12, 7, 10, 7), (24, 20, 6, 5, 1), (5, 4, 1, 1, 3),
+                                            (64, 32, 12, 14, 3)])
+def test_oracle_conv_equals_caffe_im2col_gemm(cin, cout, h, w, k):
+    """oracle/ref_net.py's Convolution (torch conv2d, padding k//2) == Caffe's own im2col_cpu (object code of
+    3rdparty/caffe/src/caffe/util/im2col.cpp) followed by the GEMM + bias of base_conv_layer.cpp:258-281, to 1e-5."""
+    import torch.nn.functional as F
+    L, fp = _ref_caffe()
+    rng = np.random.default_rng(cin * 100 + k)
+    x = rng.normal(0, 1, (cin, h, w)).astype(np.float32)
+    wt = (rng.normal(0, 1, (cout, cin, k, k)) / np.sqrt(cin * k * k)).astype(np.float32)
+    b = rng.uniform(-0.1, 0.1, cout).astype(np.float32)
+    out = np.empty((cout, h, w), np.float32)
+    L.refcaffe_conv(out.ctypes.data_as(fp), x.ctypes.data_as(fp), wt.ctypes.data_as(fp), b.ctypes.data_as(fp), cin, cout, h,
+                    w, k, k // 2)
+    want = F.conv2d(torch.from_numpy(x)[None], torch.from_numpy(wt), torch.from_numpy(b), padding=k // 2)[0].numpy()
+    assert np.abs(out - want).max() <= 1e-5 * max(1.0, np.abs(want).max())
+
+
+@pytest.mark.parametrize("h,w", [(8, 8), (9, 11), (7, 6), (1, 5), (46, 82), (23, 41)])
+def test_oracle_max_pool_equals_caffe_forward(h, w):
+    """oracle/ref_net.py's Pooling (max_pool2d 2x2 / 2, ceil_mode) == PoolingLayer::Forward_cpu as restated from
+    pooling_layer.cpp:91-111,141-175 (ceil shape rule, windows clipped to the image), bit for bit."""
+    import torch.nn.functional as F
+    L, fp = _ref_caffe()
+    rng = np.random.default_rng(h * 100 + w)
+    x = rng.normal(0, 1, (3, h, w)).astype(np.float32)
+    shape = L.refcaffe_max_pool(None, x.ctypes.data_as(fp), 3, h, w, 2, 2, 0)
+    ph, pw = shape >> 16, shape & 0xFFFF
+    out = np.empty((3, ph, pw), np.float32)
+    L.refcaffe_max_pool(out.ctypes.data_as(fp), x.ctypes.data_as(fp), 3, h, w, 2, 2, 0)
+    want = F.max_pool2d(torch.from_numpy(x)[None], 2, 2, 0, ceil_mode=True)[0].numpy()
+    assert want.shape == out.shape and np.array_equal(out, want)
