@@ -196,3 +196,23 @@ def test_reference_extractor_with_net_two_scales(tmp_path, port, cuda):
     assert out["heatblob"].shape == (1, 78, 128, 192)
     assert np.abs(out["heatblob"][0] - want).max() <= 2e-2
     _check_chain_cpu(out, out["heatblob"][0], 0, 25, (384, 256), port)
+
+
+@pytest.mark.parametrize("scale_mode", [pe.ScaleMode.ZeroToOne, pe.ScaleMode.PlusMinusOne, pe.ScaleMode.UnsignedChar,
+                                        pe.ScaleMode.NoScale, pe.ScaleMode.ZeroToOneFixedAspect,
+                                        pe.ScaleMode.PlusMinusOneFixedAspect])
+@pytest.mark.parametrize("types", [PARTS, PARTS | BKG | PAFS, BKG | PAFS])
+def test_heatmap_export_kernel_equals_reference_get_heat_maps_copy(tmp_path, port, cuda, scale_mode, types):
+    """f2: opb200_heatmaps_export (one kernel) == the reference's own PoseExtractorNet::getHeatMapsCopy
+    (poseExtractorNet.cpp:106-243, compiled unmodified into the harness) on the same heat-map blob, bit for bit."""
+    from openpose_b200 import post
+    maps, _ = synth.planted_maps(0, 46, 82, 4, seed=321, sigma=1.2, paf_halfwidth=0.8, noise=0.02, limb_len=(3.0, 7.0))
+    maps[3] *= 1.7                                    # values beyond [0, 1] / [-1, 1]: the clamps matter
+    maps[40] *= -2.5
+    x = np.zeros((1, 3, 368, 656), np.float32)
+    out = run_extractor(tmp_path, 0, [x], [1.0], (1280, 720), net_output=maps[None], types=types,
+                        scale_mode=int(scale_mode))
+    heat = torch.from_numpy(out["heatblob"]).to(cuda)
+    got = post.heatmaps_export_gpu(heat, 25, True, 52, types, int(scale_mode), to_host=False)[0].cpu().numpy()
+    assert got.shape == out["heatmaps"].shape
+    assert np.array_equal(got, out["heatmaps"])
