@@ -260,7 +260,8 @@ int opo_preprocess(float* dst, const unsigned char* src, int hs, int ws, int ht,
  * ------------------------------------------------------------------------------------------------ */
 static int sat_short(int v) { return v < -32768 ? -32768 : (v > 32767 ? 32767 : v); }
 
-void opo_crop_warp(float* dst, const unsigned char* frame, const double* m, int hs, int ws, int ht, int wt)
+/* the warp alone: frame (hs, ws, 3) u8 -> dst (ht, wt, 3) u8, what cv::warpAffine returns */
+void opo_warp_affine_u8(unsigned char* dst, const unsigned char* frame, const double* m, int hs, int ws, int ht, int wt)
 {
     for (int y = 0; y < ht; y++)
     {
@@ -284,10 +285,24 @@ void opo_crop_warp(float* dst, const unsigned char* frame, const double* m, int 
                 }
                 int v = (acc + (1 << 14)) >> 15;
                 v = v < 0 ? 0 : (v > 255 ? 255 : v);
-                dst[((size_t)c * ht + y) * wt + x] = (float)v * (1 / 256.f) - 0.5f;
+                dst[((size_t)y * wt + x) * 3 + c] = (unsigned char)v;
             }
         }
     }
+}
+
+/* warp + uCharCvMatToFloatPtr(normalize = 1): (3, ht, wt) fp32 = v / 256 - 0.5 */
+void opo_crop_warp(float* dst, const unsigned char* frame, const double* m, int hs, int ws, int ht, int wt)
+{
+    unsigned char* img = (unsigned char*)malloc((size_t)ht * wt * 3);
+    if (!img)
+        return;
+    opo_warp_affine_u8(img, frame, m, hs, ws, ht, wt);
+    for (int c = 0; c < 3; c++)
+        for (int y = 0; y < ht; y++)
+            for (int x = 0; x < wt; x++)
+                dst[((size_t)c * ht + y) * wt + x] = (float)img[((size_t)y * wt + x) * 3 + c] * (1 / 256.f) - 0.5f;
+    free(img);
 }
 
 /* ------------------------------------------------------------------------------------------------

@@ -42,11 +42,13 @@
 
 namespace op
 {
+#ifndef OPB_REF_SHIM_NO_MATRIX   // (the hand / face harness links the reference's real core/matrix.cpp instead)
     // (2) Matrix(): an empty handle is all Array<T> needs.
     Matrix::Matrix() {}
     // (6) only referenced by fileStream.cpp's image / FileStorage helpers, which the oracle never calls
     Matrix::Matrix(const void*) { std::abort(); }
     const void* Matrix::getConstCvMat() const { std::abort(); }
+#endif
 
     // (1) Array<T> members. Storage semantics: row-major, owned by a shared_ptr<T[]>.
     template<typename T>
@@ -89,6 +91,12 @@ namespace op
     Array<T>::Array(const std::vector<int>& sizes)
     {
         reset(sizes);
+    }
+
+    template<typename T>
+    Array<T>::Array(const std::vector<int>& sizes, const T value)   // array.cpp:126-136
+    {
+        reset(sizes, value);
     }
 
     template<typename T>
@@ -170,11 +178,13 @@ namespace op
         std::abort();
     }
 
+#ifndef OPB_REF_SHIM_NO_MATRIX
     void* Matrix::getCvMat()
     {
         std::fprintf(stderr, "oracle shim: Matrix::getCvMat reached (rendering) - out of scope\n");
         std::abort();
     }
+#endif
 
 #define OPREF_INSTANTIATE_ARRAY(T) \
     template Array<T>::Array(const Array<T>&, const int, const bool); \
@@ -182,6 +192,7 @@ namespace op
     template size_t Array<T>::getVolume(const int, const int) const; \
     template Matrix& Array<T>::getCvMat(); \
     template Array<T>::Array(const std::vector<int>&); \
+    template Array<T>::Array(const std::vector<int>&, const T); \
     template void Array<T>::reset(const int); \
     template void Array<T>::reset(const std::vector<int>&); \
     template void Array<T>::reset(const std::vector<int>&, const T); \
