@@ -145,8 +145,15 @@ namespace opb
             }
         };
 
-        bool parseNode(Lexer& lx, Node& node, char closer, std::string& err)
+        constexpr int kMaxNesting = 64;   // a prototxt nests 3-4 deep; a file of repeated '{' must not overflow the stack
+
+        bool parseNode(Lexer& lx, Node& node, char closer, std::string& err, int depth = 0)
         {
+            if (depth > kMaxNesting)
+            {
+                err = "prototxt: messages nested deeper than 64 levels";
+                return false;
+            }
             for (;;)
             {
                 if (lx.eof())
@@ -174,7 +181,7 @@ namespace opb
                     std::string t;
                     lx.token(t, err);
                     f.msg = std::make_shared<Node>();
-                    if (!parseNode(lx, *f.msg, c == '{' ? '}' : '>', err))
+                    if (!parseNode(lx, *f.msg, c == '{' ? '}' : '>', err, depth + 1))
                         return false;
                 }
                 else if (!lx.token(f.scalar, err))
@@ -248,9 +255,15 @@ namespace opb
                     const Node& c = *pp->msg;
                     const std::string m = c.str("pool", "MAX");
                     d.poolMethod = (m == "MAX" || m == "0") ? 0 : ((m == "AVE" || m == "1") ? 1 : 2);
-                    d.kernel = c.integer("kernel_size", 1);
-                    d.stride = c.integer("stride", 1);
-                    d.pad = c.integer("pad", 0);
+                    d.kernel = c.integer("kernel_size", c.integer("kernel_h", 1));
+                    d.stride = c.integer("stride", c.integer("stride_h", 1));
+                    d.pad = c.integer("pad", c.integer("pad_h", 0));
+                    if (c.integer("kernel_w", d.kernel) != d.kernel || c.integer("pad_w", d.pad) != d.pad ||
+                        c.integer("stride_w", d.stride) != d.stride)
+                    {
+                        err = "prototxt: non-square pooling in layer " + d.name;
+                        return false;
+                    }
                 }
             if (const Field* cc = L.first("concat_param"))
                 if (cc->msg)

@@ -57,11 +57,18 @@ namespace opb
     constexpr int kAuxBytes = 2048;
     static_assert(sizeof(ConvAux) <= kAuxBytes, "aux block too large");
 
-    // Debug timeline (OPB200_CONV_TRACE): clock64 stamps of CTA 0's roles per work item, printed by the kernel itself.
-    __device__ unsigned long long gConvTrace[16 * 16 + 2];
+    // Debug timeline (OPB200_CONV_TRACE) and ablation switches (OPB200_CONV_DEBUG): compiled only into trace builds
+    // (make TRACE=1 -> -DOPB200_CONV_TRACE_BUILD); the release kernel carries neither the stamps nor the mode tests.
+#ifdef OPB200_CONV_TRACE_BUILD
+    constexpr bool kConvDebug = true;
+#else
+    constexpr bool kConvDebug = false;
+#endif
+    // clock64 stamps of CTA 0's roles per work item, printed by the kernel itself
+    __device__ unsigned long long gConvTrace[kConvDebug ? 16 * 16 + 2 : 1];
     __device__ __forceinline__ void traceStamp(bool on, int slot, int work)
     {
-        if (on && work < 16)
+        if (kConvDebug && on && work < 16)
             reinterpret_cast<volatile unsigned long long*>(gConvTrace)[slot * 16 + work] = clock64();
     }
 
@@ -168,7 +175,7 @@ namespace opb
         // everything above touched only kernel parameters, smem and TMEM; from here on we read the previous
         // layer's output and overwrite buffers it may still be reading
         asm volatile("griddepcontrol.wait;" ::: "memory");
-        const bool traceOn = (p.debugMode & 4) && blockIdx.x == 0;
+        const bool traceOn = kConvDebug && (p.debugMode & 4) && blockIdx.x == 0;
         if (traceOn && threadIdx.x == 0)
             reinterpret_cast<volatile unsigned long long*>(gConvTrace)[256] = clock64();
 
@@ -325,7 +332,7 @@ namespace opb
                                 mbarWait(&aux->bFull[bs], bPhase);
                                 tcFenceAfter();
                                 const uint64_t bDesc = bBase + (uint64_t)(bs * p.bGroup * (kBStageBytes >> 4));
-                                if (leader && !(p.debugMode & 2))
+                                if (leader && !(kConvDebug && (p.debugMode & 2)))
                                 {
                                     if (p.bGroup == 3)
                                         mmaGroupBf16<3, PAIR>(tmemD0, tmemD1, aDesc0, aDesc1, bDesc, (uint32_t)kyStep,
@@ -455,7 +462,7 @@ namespace opb
                     const bool inImage = (x < p.W) && (y < p.H);
                     const bool isSeparator = p.flatPitch != 0 && (x % p.flatPitch) == p.flatW;
 #pragma unroll 1
-                    for (int q = half; q < kPieces && !(p.debugMode & 1); q += 2)
+                    for (int q = half; q < kPieces && !(kConvDebug && (p.debugMode & 1)); q += 2)
                     {
                         uint32_t v[32];
                         tmemLoad32(taddr + q * 32, v);

@@ -200,3 +200,19 @@ def test_oracle_max_pool_equals_caffe_forward(h, w):
     L.refcaffe_max_pool(out.ctypes.data_as(fp), x.ctypes.data_as(fp), 3, h, w, 2, 2, 0)
     want = F.max_pool2d(torch.from_numpy(x)[None], 2, 2, 0, ceil_mode=True)[0].numpy()
     assert want.shape == out.shape and np.array_equal(out, want)
+
+
+def test_prototxt_hostile_nesting_and_anisotropic_pooling(tmp_path):
+    """the C++ reader caps message nesting (no stack overflow on a file of '{') and rejects non-square pooling windows
+    instead of silently planning them as 1x1 (the conv path already rejects non-square kernels)."""
+    _, cm, _, _ = __import__("openpose_b200.modelgen", fromlist=["build_files"]).build_files("body_25", 1234)
+    bad = tmp_path / "nest.prototxt"
+    bad.write_text("layer " + "{ a " * 20000)
+    with pytest.raises(Opb200Error, match="nested deeper"):
+        netmod.describe(str(bad), cm)
+    pool = tmp_path / "pool.prototxt"
+    pool.write_text('input: "image"\ninput_dim: 1\ninput_dim: 3\ninput_dim: 16\ninput_dim: 16\n'
+                    'layer { name: "p" type: "Pooling" bottom: "image" top: "net_output" '
+                    'pooling_param { pool: MAX kernel_h: 2 kernel_w: 3 stride: 2 } }\n')
+    with pytest.raises(Opb200Error, match="non-square pooling"):
+        netmod.describe(str(pool), cm)
