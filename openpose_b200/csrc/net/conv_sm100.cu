@@ -49,6 +49,7 @@ namespace opb
         uint64_t aFull[kMaxAStages], aEmpty[kMaxAStages];
         uint64_t bFull[kMaxBStages], bEmpty[kMaxBStages];
         uint64_t tmemFull[2], tmemEmpty[2];
+        uint64_t stFull[2], stEmpty[2];       // output staging buffers: written by the epilogue warps, drained by the store warp
         uint32_t tmemBase;
         uint32_t pad;
         alignas(16) float bias[128];          // bias of the current Cout tile (read as float4)
@@ -155,6 +156,8 @@ namespace opb
             {
                 mbarInit(&aux->tmemFull[i], 1);
                 mbarInit(&aux->tmemEmpty[i], PAIR ? 512 : 256);   // every epilogue thread (of both CTAs) arrives
+                mbarInit(&aux->stFull[i], 8);                     // one arrival per epilogue warp
+                mbarInit(&aux->stEmpty[i], 1);
             }
             fenceBarrierInit();
         }
@@ -404,12 +407,12 @@ namespace opb
             const int t = quad * 32 + lane;           // 0..127 = TMEM lane = pixel of the tile
             const int et = threadIdx.x - 128;         // 0..255 over all epilogue threads
             const int tw = t % kConvTileW, th = t / kConvTileW;
-            const uint32_t halfBar = 2 + half;        // named barrier of this half (128 threads)
-            const bool issuer = (quad == 0 && lane == 0);
             constexpr int kPieces = BN / 32;
             int acc = 0;
             uint32_t accPhase = 0;
             int lastNt = -1;
+            const bool stores = (p.storeBf16 | p.poolFused) != 0;
+            uint32_t stUses[2] = {0u, 0u};
             for (int work = workStart; work < numWork; work += workStride)
             {
                 const int item = p.reverse ? numWork - 1 - work : work;
@@ -439,23 +442,12 @@ namespace opb
                     if (mt >= p.numMTiles)
                         break;                         // odd tile count: the last pair has no second tile
                     const TileCoord tc = tileCoord(p, mt);
-                    // this half's staging pieces are free once its previous TMA stores have read them
-                    if (p.storeBf16 | p.poolFused)
-                    {
-                        // (two staging buffers, one per tile of the item: only the stores of the tile before the previous
-                        // one must have drained -- a TMA store waits behind every load the producers have queued)
-                        if (issuer)
-                        {
-                            if (p.stagingBufs == 2)
-                                tmaStoreWaitRead1();
-                            else
-                                tmaStoreWaitRead0();
-                        }
-                        namedBarrier(halfBar, 128);
-                    }
-                    traceStamp(traceOn && et == 0, 8 + 2 * j, wi);
-                    // staging buffer of this tile: one per tile of the item, or alternating between single-tile items
+                    // staging buffer of this tile: one per tile of the item, or alternating between single-tile items. It is
+                    // free once the store warp's TMA stores of its previous use have read it.
                     const int sbuf = p.stagingBufs == 2 ? (two ? j : (wi & 1)) : 0;
+                    if (stores)
+                        mbarWait(&aux->stEmpty[sbuf], ((stUses[sbuf] & 1u) ^ 1u));
+                    traceStamp(traceOn && et == 0, 8 + 2 * j, wi);
                     const uint32_t taddr =
                         tmemBase + (acc * 2 + j) * Cfg::kAccStride + ((uint32_t)(quad * 32) << 16);
                     const int x = tc.x0 + tw, y = tc.y0 + th;
@@ -604,27 +596,17 @@ namespace opb
                             mbarArrive(&aux->tmemEmpty[acc]);
                         released = true;
                     }
-                    if (p.storeBf16 | p.poolFused)
+                    if (stores)
                     {
+                        // hand the staged tile to the store warp: a TMA store queues behind every load the producers have in
+                        // flight (the issuing thread sits 1.5-4 k cycles in the instruction), which used to hold up all
+                        // epilogue warps at the next barrier -- now only the store warp waits
                         fenceProxyAsyncShared();
-                        namedBarrier(halfBar, 128);
+                        __syncwarp();
+                        if (lane == 0)
+                            mbarArrive(&aux->stFull[sbuf]);
+                        ++stUses[sbuf];
                         traceStamp(traceOn && lane == 0 && wi == 1 && j == 1, 13, warp - 4);
-                        if (issuer)
-                        {
-                            // pooled: oMap describes the pooled blob with a (32 ch, 4, 8) box
-                            const int sx = p.poolFused ? tc.x0 >> 1 : tc.x0, sy = p.poolFused ? tc.y0 >> 1 : tc.y0;
-                            for (int q = half; q < kPieces; q += 2)
-                                if (nt * BN + q * 32 < p.cout)
-                                {
-                                    const void* src = sOut + sbuf * Cfg::kStagingBytes + q * (kConvBlockM * 64);
-                                    const int c0 = nt * BN + q * 32;
-                                    if (p.poolFused && p.poolOutFlat)   // per-frame map of a flat level: (c, x, n, y)
-                                        tmaStore4d(&p.oMap, src, c0, sx, tc.n, sy);
-                                    else
-                                        tmaStore4d(&p.oMap, src, c0, sx, sy, tc.n);
-                                }
-                            tmaStoreCommit();
-                        }
                     }
                 }
                 if (!released)   // no tile of this item belongs to this CTA (ragged end of a quad)
@@ -642,8 +624,54 @@ namespace opb
                     accPhase ^= 1;
                 }
             }
-            if (issuer)
-                tmaStoreWaitAll();   // (waiting only for the stores' smem reads was measured: no gain, so the stronger wait stays)
+        }
+        else if (warp == 2 && (p.storeBf16 | p.poolFused))
+        {
+            // ====================================== store warp ========================================
+            // (the TMEM allocator warp, idle in between) walks the same tiles as the epilogue warps: waits for a staged
+            // tile, issues its TMA stores, and frees the staging buffer once the stores have read it
+            constexpr int kPieces = BN / 32;
+            const bool leader = electOne();
+            uint32_t stUses[2] = {0u, 0u};
+            for (int work = workStart; work < numWork; work += workStride)
+            {
+                const int item = p.reverse ? numWork - 1 - work : work;
+                const int nt = item % p.nTilesN;
+                const int pair = PAIR ? 2 * (item / p.nTilesN) + (int)ctaRank : item / p.nTilesN;
+                const int wi = (work - workStart) / workStride;
+                for (int j = 0; j < tpi; ++j)
+                {
+                    const int mt = tpi * pair + j;
+                    if (mt >= p.numMTiles)
+                        break;
+                    const TileCoord tc = tileCoord(p, mt);
+                    const int sbuf = p.stagingBufs == 2 ? (two ? j : (wi & 1)) : 0;
+                    mbarWait(&aux->stFull[sbuf], stUses[sbuf] & 1u);
+                    if (leader)
+                    {
+                        // pooled: oMap describes the pooled blob with a (32 ch, 4, 8) box
+                        const int sx = p.poolFused ? tc.x0 >> 1 : tc.x0, sy = p.poolFused ? tc.y0 >> 1 : tc.y0;
+                        for (int q = 0; q < kPieces; ++q)
+                            if (nt * BN + q * 32 < p.cout)
+                            {
+                                const void* src = sOut + sbuf * Cfg::kStagingBytes + q * (kConvBlockM * 64);
+                                const int c0 = nt * BN + q * 32;
+                                if (p.poolFused && p.poolOutFlat)   // per-frame map of a flat level: (c, x, n, y)
+                                    tmaStore4d(&p.oMap, src, c0, sx, tc.n, sy);
+                                else
+                                    tmaStore4d(&p.oMap, src, c0, sx, sy, tc.n);
+                            }
+                        tmaStoreCommit();
+                        tmaStoreWaitRead0();
+                        mbarArrive(&aux->stEmpty[sbuf]);
+                    }
+                    __syncwarp();
+                    ++stUses[sbuf];
+                }
+            }
+            if (leader)
+                tmaStoreWaitAll();
+            __syncwarp();
         }
         tcFenceBefore();
         if (traceOn)
