@@ -16,6 +16,7 @@
 #include "../common.cuh"
 #include "bicubic.cuh"
 #include <algorithm>
+#include <cstdlib>
 
 namespace opb
 {
@@ -110,6 +111,141 @@ namespace opb
                     o.w = cubicEval(Aw, Bw, Cw, t1.w, dy);
                     *reinterpret_cast<float4*>(dp + (size_t)y * wt + 4 * q) = o;
                 }
+            }
+        }
+    }
+
+    // ------------------------------------------------------------------------------------------------
+    // x8 single-scale kernel, register-streaming form. A thread owns FOUR adjacent output columns (they share their four
+    // x taps: columns 8k+4 .. 8k+11 have floor(xs) = k) of one plane and walks down a run of y-groups. Per y-group it
+    // needs the x-pass of four source rows for its columns; consecutive groups shift that window by one row, so one new
+    // source row (4 loads, one cubic coefficient set, 4 evaluations) is computed per group and the rest lives in
+    // registers. Then the polynomial coefficients of its 4 columns (once per group) and 8 rows x 4 evaluations, stored as
+    // 8 float4 (a warp writes 512 contiguous bytes per row). No shared memory, no barriers, no idle lanes: every
+    // operation is the one resize8Kernel performs, in the same order, so the result is the same bit for bit.
+    // ------------------------------------------------------------------------------------------------
+    constexpr int kR8sThreads = 256;
+
+    __device__ __forceinline__ void xPassRow(float out[4], float v0, float v1, float v2, float v3, const float dx[4])
+    {
+        const float A = cubicA(v0, v1, v2, v3), B = cubicB(v0, v1, v2, v3), C = cubicC(v0, v2);
+#pragma unroll
+        for (int e = 0; e < 4; e++)
+            out[e] = cubicEval(A, B, C, v1, dx[e]);
+    }
+
+    __global__ void __launch_bounds__(kR8sThreads) resize8StreamKernel(float* __restrict__ dst, const float* __restrict__ src,
+                                                                     long long planes, int hs, int ws, int ht, int wt,
+                                                                     int chunks)
+    {
+        const int quads = wt >> 2;
+        const long long perChunk = planes * quads;
+        const long long t = (long long)blockIdx.x * kR8sThreads + threadIdx.x;
+        if (t >= perChunk * chunks)
+            return;
+        const int chunk = (int)(t / perChunk);
+        const long long idx = t - (long long)chunk * perChunk;
+        const long long plane = idx / quads;
+        const int q = (int)(idx - plane * quads);
+        const float* __restrict__ sp = src + plane * hs * ws;
+        float* __restrict__ dp = dst + plane * (long long)ht * wt + 4 * q;
+        // x taps of the quad: columns 4q .. 4q+3 lie in x-group gx = floor(xs)
+        const int gx = (q & 1) ? (q - 1) >> 1 : (q >> 1) - 1;
+        const int x1 = min(ws - 1, max(0, gx));
+        const int x0 = max(0, x1 - 1), x2 = min(ws - 1, x1 + 1), x3 = min(ws - 1, x2 + 1);
+        float dx[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++)
+            dx[e] = sub(srcCoord8(4 * q + e), (float)x1);
+        // y-groups g = -1 .. hs-1 (rows 8g+4 .. 8g+11), split evenly over the chunks
+        const int groups = hs + 1;
+        const int gBegin = (int)((long long)groups * chunk / chunks) - 1;
+        const int gEnd = (int)((long long)groups * (chunk + 1) / chunks) - 1;
+        float W[4][4];     // x-pass of source rows min(hs-1, lo + i) for this quad
+        int lo = 0;
+        if (gBegin < gEnd)
+        {
+            lo = max(0, min(hs - 1, max(0, gBegin)) - 1);
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+            {
+                const float* row = sp + (size_t)min(hs - 1, lo + i) * ws;
+                xPassRow(W[i], __ldg(row + x0), __ldg(row + x1), __ldg(row + x2), __ldg(row + x3), dx);
+            }
+        }
+        for (int g = gBegin; g < gEnd; g++)
+        {
+            const int y1 = min(hs - 1, max(0, g));
+            const int y0 = max(0, y1 - 1);            // == lo
+            // the next group's window is this one or this one shifted down a row: fetch the taps of the incoming row now,
+            // so that their latency hides behind this group's evaluations (ncu: the first use of these taps is still where
+            // 44 % of the stall samples land -- reads queue behind this SM's own stores -- and an L2 prefetch eight rows
+            // ahead changes nothing, so it is not a DRAM miss; see profiles/r02_resize8_stream_ncu.txt)
+            const bool shiftNext = (g + 1 < gEnd) && (max(0, min(hs - 1, g + 1) - 1) != lo);
+            float n0 = 0.f, n1 = 0.f, n2 = 0.f, n3 = 0.f;
+            if (shiftNext)
+            {
+                const float* row = sp + (size_t)min(hs - 1, lo + 4) * ws;
+                n0 = __ldg(row + x0), n1 = __ldg(row + x1), n2 = __ldg(row + x2), n3 = __ldg(row + x3);
+            }
+            // taps (y0, y1, y2, y3) = rows (lo, lo+1, lo+2, lo+3) clamped to hs-1, except at the top where y1 == y0 == 0
+            const bool top = (y1 == y0);
+            float A[4], B[4], C[4], v1[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++)
+            {
+                const float t0 = W[0][e];
+                const float t1 = top ? W[0][e] : W[1][e];
+                const float t2 = top ? W[1][e] : W[2][e];
+                const float t3 = top ? W[2][e] : W[3][e];
+                A[e] = cubicA(t0, t1, t2, t3);
+                B[e] = cubicB(t0, t1, t2, t3);
+                C[e] = cubicC(t0, t2);
+                v1[e] = t1;
+            }
+            // rows 8g+4+r, r = 0..7 (the first group keeps r >= 4, the last r < 4). srcCoord8 is exact in float (y + 0.5, x 0.125
+            // and - 0.5 lose no bits), so dy = srcCoord8(y) - y1 is exactly (r + 0.5) / 8 + (g - y1): a constant per r, and
+            // g - y1 is -1 in the first group and 0 elsewhere.
+            const size_t rowStride = (size_t)wt;
+            float* __restrict__ op = dp + (size_t)(8 * g + 4) * rowStride;
+            if (g >= 0 && g < hs - 1)
+            {
+#pragma unroll
+                for (int r = 0; r < 8; r++)
+                {
+                    const float dy = 0.0625f * (float)(2 * r + 1);
+                    float4 o;
+                    o.x = cubicEval(A[0], B[0], C[0], v1[0], dy);
+                    o.y = cubicEval(A[1], B[1], C[1], v1[1], dy);
+                    o.z = cubicEval(A[2], B[2], C[2], v1[2], dy);
+                    o.w = cubicEval(A[3], B[3], C[3], v1[3], dy);
+                    __stcs(reinterpret_cast<float4*>(op + r * rowStride), o);   // streaming: the maps are read once, later
+                }
+            }
+            else
+            {
+                const int rBegin = max(0, -(8 * g + 4)), rEnd = min(8, ht - (8 * g + 4));
+                const float dyOff = (float)(g - y1);
+                for (int r = rBegin; r < rEnd; r++)
+                {
+                    const float dy = add(0.0625f * (float)(2 * r + 1), dyOff);
+                    float4 o;
+                    o.x = cubicEval(A[0], B[0], C[0], v1[0], dy);
+                    o.y = cubicEval(A[1], B[1], C[1], v1[1], dy);
+                    o.z = cubicEval(A[2], B[2], C[2], v1[2], dy);
+                    o.w = cubicEval(A[3], B[3], C[3], v1[3], dy);
+                    __stcs(reinterpret_cast<float4*>(op + r * rowStride), o);
+                }
+            }
+            if (shiftNext)
+            {
+#pragma unroll
+                for (int i = 0; i < 3; i++)
+#pragma unroll
+                    for (int e = 0; e < 4; e++)
+                        W[i][e] = W[i + 1][e];
+                xPassRow(W[3], n0, n1, n2, n3, dx);
+                lo++;
             }
         }
     }
@@ -314,6 +450,22 @@ extern "C" opb200_status opb200_resize_merge(float* dst, const float* const* src
         OPB_REQUIRE(wt == 8 * ws && ht == 8 * hs,
                     "Kernel only implemented for 8x resize. Notify us if this error appears.");
         const bool aligned = ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0) && (wt % 4 == 0);
+        static const bool streamKernel = !(std::getenv("OPB200_RESIZE8_STREAM") && std::atoi(std::getenv("OPB200_RESIZE8_STREAM")) == 0);
+        if (wt == 8 * ws && ht == 8 * hs && aligned && streamKernel)
+        {
+            // enough threads for >= 4 waves of 512 per SM (102 registers: 2 blocks; capping at 80 or 64 registers measured slower), in as few row chunks as possible (each chunk re-does 3 x-pass rows)
+            const long long perChunk = planes * (wt >> 2);
+            int chunks = 1;
+            while (chunks < 8 && chunks < hs + 1 && perChunk * chunks < 4ll * kNumSMsB200 * 512)
+                chunks *= 2;
+            if (chunks > hs + 1)
+                chunks = hs + 1;
+            const long long blocks = (perChunk * chunks + kR8sThreads - 1) / kR8sThreads;
+            OPB_REQUIRE(blocks < (1ll << 31), "resizeAndMerge: too many planes for one launch");
+            resize8StreamKernel<<<(unsigned)blocks, kR8sThreads, 0, st>>>(dst, srcs[0], planes, hs, ws, ht, wt, chunks);
+            OPB_LAUNCH_CHECK();
+            return OPB200_OK;
+        }
         if (wt == 8 * ws && ht == 8 * hs && aligned)
         {
             const long long blocks4 = planes * ((hs + 1 + 3) / 4);
