@@ -395,6 +395,140 @@ namespace opb
         }
     }
 
+    // ------------------------------------------------------------------------------------------------
+    // Multi-scale kernel for up-sampling factors (every scaleH >= 1: the BASELINE config-2 case), register streaming like
+    // resize8StreamKernel. A thread owns ONE output column of one plane and walks down a chunk of rows. Per scale it
+    // keeps the x-pass of the four source rows of the current y taps in registers; because the factor is >= 1 the
+    // (clamped) tap row advances by at most one per output row, so the window shifts by one and at most one new source
+    // row enters, whose four x taps were fetched when the previous one entered. The y taps / offsets of a row are
+    // block-uniform and come from a shared-memory table built once per block. Per output value and scale this leaves
+    // one table read, one uniform compare and the seven operations of the cubic; the operations and their order are
+    // the reference's (bit-exact against resizeAndAddAndAverageKernel, tests/test_refcuda_gpu.py).
+    // ------------------------------------------------------------------------------------------------
+    constexpr int kMsThreads = 256;
+    constexpr int kMsMaxRows = 256;       // rows per chunk (table size)
+    constexpr int kMsMaxScales = 4;
+
+    template <int S>
+    __global__ void __launch_bounds__(kMsThreads) resizeMergeStreamKernel(float* __restrict__ dst, const MergeArgs a,
+                                                                         long long planes, int rowsPerChunk)
+    {
+        __shared__ int2 tab[S][kMsMaxRows];   // per scale and row of the chunk: clamped floor(ys), bits of dy
+        const int yBegin = blockIdx.y * rowsPerChunk;
+        const int rows = min(rowsPerChunk, a.ht - yBegin);
+        for (int t = threadIdx.x; t < S * rows; t += kMsThreads)
+        {
+            const int s = t / rows, yy = t - s * rows;
+            int yi[4];
+            float dy;
+            taps(yi, dy, srcCoord(yBegin + yy, a.scaleH[s]), a.hs[s]);
+            tab[s][yy] = make_int2(yi[1], __float_as_int(dy));
+        }
+        __syncthreads();
+        const long long t = (long long)blockIdx.x * kMsThreads + threadIdx.x;
+        if (t >= planes * a.wt)
+            return;
+        const long long plane = t / a.wt;
+        const int x = (int)(t - plane * a.wt);
+        float* __restrict__ dp = dst + (size_t)plane * a.ht * a.wt + (size_t)yBegin * a.wt + x;
+
+        const float* sp[S];
+        int xi[S][4], cur[S];
+        float dx[S], X[S][4], P[S][4], A[S], B[S], C[S], V[S];
+#pragma unroll
+        for (int s = 0; s < S; s++)
+        {
+            const int h = a.hs[s], w = a.ws[s];
+            sp[s] = a.src[s] + (size_t)plane * h * w;
+            taps(xi[s], dx[s], srcCoord(x, a.scaleW[s]), w);
+            const int c = tab[s][0].x;
+            cur[s] = c;
+            const int r2 = min(h - 1, c + 1);
+            const int rr[4] = {max(0, c - 1), c, r2, min(h - 1, r2 + 1)};
+            float v[4][4];
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+#pragma unroll
+                for (int e = 0; e < 4; e++)
+                    v[k][e] = __ldg(sp[s] + (size_t)rr[k] * w + xi[s][e]);
+            const float* nr = sp[s] + (size_t)min(h - 1, c + 3) * w;
+#pragma unroll
+            for (int e = 0; e < 4; e++)
+                P[s][e] = __ldg(nr + xi[s][e]);
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                X[s][k] = cubic1d(v[k][0], v[k][1], v[k][2], v[k][3], dx[s]);
+            A[s] = cubicA(X[s][0], X[s][1], X[s][2], X[s][3]);
+            B[s] = cubicB(X[s][0], X[s][1], X[s][2], X[s][3]);
+            C[s] = cubicC(X[s][0], X[s][2]);
+            V[s] = X[s][1];
+        }
+        const float cnt = (float)S;
+        for (int yy = 0; yy < rows; yy++)
+        {
+            // table entries of all scales first, the (rare, block-uniform) window moves next, then S independent cubics
+            int2 e[S];
+            bool moved = false;
+#pragma unroll
+            for (int s = 0; s < S; s++)
+            {
+                e[s] = tab[s][yy];
+                moved = moved || (e[s].x != cur[s]);
+            }
+            if (moved)
+            {
+#pragma unroll
+                for (int s = 0; s < S; s++)
+                    if (e[s].x != cur[s])       // the tap row moved down by one
+                    {
+                        const int h = a.hs[s], w = a.ws[s];
+                        cur[s] = e[s].x;
+                        X[s][0] = X[s][1];
+                        X[s][1] = X[s][2];
+                        X[s][2] = X[s][3];
+                        if (e[s].x + 2 <= h - 1)    // a new source row enters (otherwise the clamped last row stays)
+                            X[s][3] = cubic1d(P[s][0], P[s][1], P[s][2], P[s][3], dx[s]);
+                        const float* nr = sp[s] + (size_t)min(h - 1, e[s].x + 3) * w;
+#pragma unroll
+                        for (int k = 0; k < 4; k++)
+                            P[s][k] = __ldg(nr + xi[s][k]);
+                        A[s] = cubicA(X[s][0], X[s][1], X[s][2], X[s][3]);
+                        B[s] = cubicB(X[s][0], X[s][1], X[s][2], X[s][3]);
+                        C[s] = cubicC(X[s][0], X[s][2]);
+                        V[s] = X[s][1];
+                    }
+            }
+            float v[S];
+#pragma unroll
+            for (int s = 0; s < S; s++)
+                v[s] = cubicEval(A[s], B[s], C[s], V[s], __int_as_float(e[s].y));
+            float acc = 0.f;
+#pragma unroll
+            for (int s = 0; s < S; s++)
+                acc = add(acc, v[s]);
+            // (a division by 2 or 4 is the same float as the multiplication by 0.5 or 0.25)
+            dp[(size_t)yy * a.wt] = (S == 2 || S == 4) ? mul(acc, 1.f / (float)S) : divf(acc, cnt);
+        }
+    }
+
+    template <int S>
+    static cudaError_t launchMergeStream(float* dst, const MergeArgs& a, long long planes, cudaStream_t st)
+    {
+        // chunks: at most kMsMaxRows rows each, and enough of them for ~3 x 512 threads per SM (BODY_25 frame: 5 chunks of
+        // 74 rows; 2-4 chunks measure 0-7 % slower, 8-16 chunks 7-30 % slower: each chunk pays 4 blocking x-pass rows per scale)
+        const long long cols = planes * a.wt;
+        int chunks = (a.ht + kMsMaxRows - 1) / kMsMaxRows;
+        const int want = (int)std::min<long long>((3ll * kNumSMsB200 * 512 + cols - 1) / cols, (long long)std::max(1, a.ht / 16));
+        chunks = std::max(chunks, want);
+        const int rowsPerChunk = (a.ht + chunks - 1) / chunks;
+        chunks = (a.ht + rowsPerChunk - 1) / rowsPerChunk;
+        const long long bx = (cols + kMsThreads - 1) / kMsThreads;
+        if (bx >= (1ll << 31) || chunks > 65535)
+            return cudaErrorInvalidConfiguration;
+        resizeMergeStreamKernel<S><<<dim3((unsigned)bx, (unsigned)chunks), kMsThreads, 0, st>>>(dst, a, planes, rowsPerChunk);
+        return cudaPeekAtLastError();
+    }
+
     template <int G>
     static cudaError_t launch8(float* dst, const float* src, int planes, int hs, int ws, int ht, int wt, cudaStream_t st)
     {
@@ -502,6 +636,18 @@ extern "C" opb200_status opb200_resize_merge(float* dst, const float* const* src
         a.ws[i] = src_shapes[i][3];
     }
     a.maxTmpRows = kMaxTmpRows;
+    bool upsampling = n_scales >= 2 && n_scales <= kMsMaxScales;
+    for (int i = 0; i < n_scales; i++)
+        upsampling = upsampling && a.scaleH[i] >= 1.f;
+    static const bool streamMerge = !(std::getenv("OPB200_RESIZE_MERGE_STREAM") && std::atoi(std::getenv("OPB200_RESIZE_MERGE_STREAM")) == 0);
+    if (upsampling && streamMerge)
+    {
+        cudaError_t e = n_scales == 2 ? launchMergeStream<2>(dst, a, planes, st)
+                      : n_scales == 3 ? launchMergeStream<3>(dst, a, planes, st)
+                                      : launchMergeStream<4>(dst, a, planes, st);
+        OPB_CUDA(e);
+        return OPB200_OK;
+    }
     const dim3 grid((ht + kBandRows - 1) / kBandRows, (unsigned)planes);
     resizeMergeKernel<<<grid, kGenThreads, 0, st>>>(dst, a);
     OPB_LAUNCH_CHECK();

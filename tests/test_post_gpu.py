@@ -178,6 +178,23 @@ def test_resize_multiscale_matches_oracle(port, cuda):
     assert np.array_equal(dst[0].cpu().numpy(), want)
 
 
+@pytest.mark.parametrize("sizes,ratios,target,planes", [
+    ([(5, 7), (3, 4), (1, 2)], [1.0, 0.6, 0.2], (40, 56), 5),          # tiny / one-row sources, three scales
+    ([(2, 3), (2, 2)], [1.0, 0.75], (16, 24), 3),                      # every tap clamps
+    ([(40, 30), (29, 22)], [1.0, 0.73], (330, 245), 2),                # odd target width, several row chunks
+    ([(8, 8), (64, 64)], [1.0, 16.0], (16, 16), 3),                    # second scale down-samples: band kernel
+    ([(6, 6)] * 5, [1.0, 0.9, 0.8, 0.7, 0.6], (48, 48), 2),            # five scales: band kernel
+])
+def test_resize_multiscale_ragged_matches_oracle(port, cuda, sizes, ratios, target, planes):
+    """the streaming multi-scale kernel (2-4 up-sampling scales) and the band kernel it falls back to, on ragged shapes."""
+    rng = np.random.default_rng(11)
+    srcs = [rng.normal(0, 1, size=(1, planes, h, w)).astype(np.float32) for h, w in sizes]
+    dst = torch.full((1, planes) + target, 7.0, device=cuda)
+    post.resize_and_merge_gpu(dst, [torch.from_numpy(s).to(cuda) for s in srcs], ratios)
+    want = port.resize_merge([s[0] for s in srcs], target[0], target[1], ratios)
+    assert np.array_equal(dst[0].cpu().numpy(), want)
+
+
 def test_resize_errors_and_copy(cuda):
     src = torch.randn((1, 3, 10, 12), device=cuda)
     dst = torch.empty((1, 3, 10, 12), device=cuda)
