@@ -60,8 +60,8 @@ def load_peaks():
 
 def conv_traffic(batch: int):
     """dram__bytes_read.sum + dram__bytes_write.sum over the conv launches of one step, from the committed ncu capture
-    of this command at the same batch (profiles/r01_conv_traffic.json); None when there is no capture for this batch."""
-    p = os.path.join(ROOT, "profiles", "r01_conv_traffic.json")
+    of this command at the same batch (profiles/r02_conv_traffic.json); None when there is no capture for this batch."""
+    p = os.path.join(ROOT, "profiles", "r02_conv_traffic.json")
     try:
         with open(p) as f:
             d = json.load(f)
@@ -420,7 +420,7 @@ def run_gpu(args):
         roof = {"bound": "tensor", "kernel": "whole net forward of one step: input copy + first conv + 113 conv_igemm_tcgen05 launches",
                 "achieved": achieved, "peak": peaks_tbl["tf_sustained"], "unit": "TFLOP/s",
                 "frac": achieved / peaks_tbl["tf_sustained"], "frac_of_burst_peak": achieved / peaks_tbl["tf_burst"],
-                "traffic": conv_traffic(B), "traffic_source": "committed ncu capture profiles/r01_conv_traffic.json "
+                "traffic": conv_traffic(B), "traffic_source": "committed ncu capture profiles/r02_conv_traffic.json "
                 "(not measured in this run)" if conv_traffic(B) is not None else None,
                 "peak_source": peaks_tbl["source"] + " sustained bf16 (burst %.0f)" % peaks_tbl["tf_burst"],
                 "launch_ms": conv_ms}
