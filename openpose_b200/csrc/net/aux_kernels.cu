@@ -7,6 +7,7 @@
 #include "../common.cuh"
 #include <climits>
 #include "net_kernels.h"
+#include <cstdlib>
 #include <cuda_bf16.h>
 
 namespace opb
@@ -331,9 +332,168 @@ namespace opb
         }
     }
 
+    // ----------------------------------------------------------------------------------------------------
+    // The shape every shipped graph starts with -- 3 channels, 3x3, pad 1, 64 outputs, ReLU -- with the input patch of a
+    // unit (3 channels x 3 rows x 34 columns) staged in shared memory by 4-byte cp.async (zero fill outside the image =
+    // the padding), double buffered per warp: the copies of the warp's NEXT unit are in flight while it gathers its A
+    // fragments from shared memory, runs the 32 MMAs and writes its 4 KB of output. In the generic kernel above the
+    // first use of the gathered global loads was where a third of all stall samples landed (ncu, round 2), and the
+    // per-n-tile slope / bounds handling tripled the instruction count.
+    // ----------------------------------------------------------------------------------------------------
+    constexpr int kF3PatchW = 34;                       // 32 pixels + the halo column either side
+    constexpr int kF3Patch = 9 * kF3PatchW;             // floats per staged patch: (channel, row) x column
+    constexpr int kF3Fill = (kF3Patch + 31) / 32;       // cp.async per lane and unit
+    constexpr int kF3SmemBytes = kFirstWarps * (32 * kFirstPitch + 2 * kF3Patch * 4);
+
+    __device__ __forceinline__ void cpAsync4(uint32_t dstSmem, const float* src, uint32_t srcBytes)
+    {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dstSmem), "l"(src), "r"(srcBytes) : "memory");
+    }
+
+    __global__ void __launch_bounds__(kFirstWarps * 32, 2) firstConv3x3Kernel(
+        __nv_bfloat16* __restrict__ dst, const float* __restrict__ src, const uint32_t* __restrict__ wfrag,
+        const float* __restrict__ bias, int N, int H, int W, int dstStride)
+    {
+        extern __shared__ __align__(16) uint8_t smemF3[];
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        const int g = lane >> 2, q = lane & 3;
+        uint8_t* st = smemF3 + warp * (32 * kFirstPitch);
+        float* patch = reinterpret_cast<float*>(smemF3 + kFirstWarps * 32 * kFirstPitch) + warp * 2 * kF3Patch;
+        const uint32_t patchAddr = (uint32_t)__cvta_generic_to_shared(patch);
+        // B fragments of all (n-tile, k-step) pairs: 32 registers; bias of this lane's two channels of every n-tile
+        uint32_t wb[8][2][2];
+        float2 biasReg[8];
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt)
+        {
+#pragma unroll
+            for (int s = 0; s < 2; ++s)
+            {
+                const uint2 v = __ldg(reinterpret_cast<const uint2*>(wfrag) + (nt * 2 + s) * 32 + lane);
+                wb[nt][s][0] = v.x;
+                wb[nt][s][1] = v.y;
+            }
+            biasReg[nt] = __ldg(reinterpret_cast<const float2*>(bias) + nt * 4 + q);
+        }
+        // the 8 patch elements this thread gathers per pixel: j = 16*s + 2*q + {0,1,8,9}, j = (c*3 + r)*3 + dx
+        int pOff[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+        {
+            const int j = 16 * (e >> 2) + 2 * q + (e & 1) + ((e >> 1) & 1) * 8;
+            pOff[e] = j < 27 ? (j / 3) * kF3PatchW + j % 3 : -1;      // K padding: contributes zero
+        }
+        // the patch elements this lane copies per unit: i = lane + 32*m -> (channel*3 + row, column)
+        int fOff[kF3Fill];          // global offset relative to the unit's first pixel, or INT_MIN past the patch
+#pragma unroll
+        for (int m = 0; m < kF3Fill; ++m)
+        {
+            const int i = lane + 32 * m;
+            const int cr = i / kF3PatchW, col = i - cr * kF3PatchW;
+            const int c = cr / 3, r = cr - c * 3;
+            fOff[m] = i < kF3Patch ? c * H * W + (r - 1) * W + (col - 1) : INT_MIN;
+        }
+        const int xBlocks = (W + 31) >> 5;
+        const int units = N * H * xBlocks;
+        const int stride = gridDim.x * kFirstWarps;
+        int rowNext = 0, x0Next = 0;      // position of the unit whose copies were issued last
+        auto fill = [&](int u, int buf) {
+            const int row = u / xBlocks, xb = u - row * xBlocks;
+            const int n = row / H, y = row - n * H;
+            const int x0 = xb << 5;
+            rowNext = row;
+            x0Next = x0;
+            const float* base = src + (size_t)n * 3 * H * W + (size_t)y * W + x0;
+            const uint32_t dstBase = patchAddr + (uint32_t)buf * (kF3Patch * 4);
+            const bool interior = (y >= 1) && (y < H - 1) && (x0 >= 1) && (x0 + 32 < W);
+            if (interior)
+            {
+#pragma unroll
+                for (int m = 0; m < kF3Fill; ++m)
+                    if (fOff[m] != INT_MIN)
+                        cpAsync4(dstBase + (uint32_t)(lane + 32 * m) * 4u, base + fOff[m], 4u);
+            }
+            else
+            {
+#pragma unroll
+                for (int m = 0; m < kF3Fill; ++m)
+                    if (fOff[m] != INT_MIN)
+                    {
+                        const int i = lane + 32 * m;
+                        const int cr = i / kF3PatchW, col = i - cr * kF3PatchW;
+                        const int yy = y + cr % 3 - 1, xx = x0 + col - 1;
+                        const bool ok = yy >= 0 && yy < H && xx >= 0 && xx < W;
+                        cpAsync4(dstBase + (uint32_t)(lane + 32 * m) * 4u, ok ? base + fOff[m] : src, ok ? 4u : 0u);
+                    }
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        int u = blockIdx.x * kFirstWarps + warp;
+        if (u < units)
+            fill(u, 0);
+        int buf = 0;
+        for (; u < units; u += stride, buf ^= 1)
+        {
+            const int row = rowNext, x0 = x0Next;
+            if (u + stride < units)
+            {
+                fill(u + stride, buf ^ 1);
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
+            }
+            else
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
+            __syncwarp();
+            const long long p0 = (long long)row * W + x0;     // first pixel of the unit in (n, y, x) raster order
+            const float* pb = patch + buf * kF3Patch;
+            uint32_t a[2][2][4];   // [m tile][k step][fragment register]
+#pragma unroll
+            for (int t = 0; t < 2; ++t)
+#pragma unroll
+                for (int hrow = 0; hrow < 2; ++hrow)
+                {
+                    const float* px = pb + t * 16 + hrow * 8 + g;
+                    float v[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e)
+                        v[e] = pOff[e] >= 0 ? px[pOff[e]] : 0.f;
+#pragma unroll
+                    for (int s = 0; s < 2; ++s)
+                    {
+                        a[t][s][hrow] = packBf16(v[4 * s + 0], v[4 * s + 1]);
+                        a[t][s][2 + hrow] = packBf16(v[4 * s + 2], v[4 * s + 3]);
+                    }
+                }
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt)
+            {
+                const float2 b2 = biasReg[nt];
+#pragma unroll
+                for (int t = 0; t < 2; ++t)
+                {
+                    float c[4] = {b2.x, b2.y, b2.x, b2.y};   // the accumulator starts at the bias
+                    mmaSyncBf16(c, a[t][0], wb[nt][0][0], wb[nt][0][1]);
+                    mmaSyncBf16(c, a[t][1], wb[nt][1][0], wb[nt][1][1]);
+                    *reinterpret_cast<uint32_t*>(st + (t * 16 + g) * kFirstPitch + nt * 16 + q * 4) = packBf16Relu(c[0], c[1]);
+                    *reinterpret_cast<uint32_t*>(st + (t * 16 + g + 8) * kFirstPitch + nt * 16 + q * 4) = packBf16Relu(c[2], c[3]);
+                }
+            }
+            __syncwarp();
+            // lane = (pixel & 3, chunk): 8 stores of 4 pixels x 128 contiguous bytes each
+            const int ch = lane & 7, pxBase = lane >> 3;
+            __nv_bfloat16* o = dst + (p0 + pxBase) * dstStride + ch * 8;
+            const uint8_t* sp = st + pxBase * kFirstPitch + ch * 16;
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+                if (x0 + pxBase + 4 * it < W)
+                    *reinterpret_cast<uint4*>(o + (long long)(4 * it) * dstStride) =
+                        *reinterpret_cast<const uint4*>(sp + 4 * it * kFirstPitch);
+            __syncwarp();      // the staging rows and this patch buffer are rewritten next
+        }
+    }
+
     opb200_status launchFirstConv(void* dst, const float* src, const uint32_t* wfrag, const float* bias,
                                   const float* slope, int N, int C, int H, int W, int k, int pad, int cout,
-                                  int dstStride, cudaStream_t st)
+                                  int dstStride, bool reluOnly, cudaStream_t st)
     {
         OPB_REQUIRE(C * k * k <= 32 && cout % 8 == 0 && cout <= 64 && dstStride % 8 == 0,
                     "first conv: needs Cin*k*k <= 32 and Cout a multiple of 8, at most 64");
@@ -341,6 +501,16 @@ namespace opb
         OPB_REQUIRE(units < (1ll << 31), "first conv: input too large");
         const long long want = (units + kFirstWarps - 1) / kFirstWarps;
         const int blocks = (int)(want < 148 * 8 ? want : 148 * 8);
+        static const bool staged = !(std::getenv("OPB200_FIRSTCONV_STAGED") && std::atoi(std::getenv("OPB200_FIRSTCONV_STAGED")) == 0);
+        if (staged && reluOnly && C == 3 && k == 3 && pad == 1 && cout == 64 && (long long)3 * H * W < (1ll << 30))
+        {
+            OPB_CUDA(cudaFuncSetAttribute(firstConv3x3Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kF3SmemBytes));
+            const int blocks3 = (int)(want < 148 * 4 ? want : 148 * 4);   // (2 to 16 blocks per SM measure the same)
+            firstConv3x3Kernel<<<blocks3 > 0 ? blocks3 : 1, kFirstWarps * 32, kF3SmemBytes, st>>>(
+                static_cast<__nv_bfloat16*>(dst), src, wfrag, bias, N, H, W, dstStride);
+            OPB_LAUNCH_CHECK();
+            return OPB200_OK;
+        }
         firstConvKernel<<<blocks > 0 ? blocks : 1, kFirstWarps * 32, 0, st>>>(
             static_cast<__nv_bfloat16*>(dst), src, wfrag, bias, slope, N, C, H, W, k, pad, cout, dstStride);
         OPB_LAUNCH_CHECK();

@@ -11,7 +11,7 @@ namespace opb
     // First layer straight from the fp32 NCHW input (Cin*k*k <= 32, Cout <= 64): mma.sync, fused bias/activation.
     opb200_status launchFirstConv(void* dstBf16Nhwc, const float* srcNchw, const uint32_t* wfrag, const float* bias,
                                   const float* slope, int N, int C, int H, int W, int k, int pad, int cout,
-                                  int dstStride, cudaStream_t st);
+                                  int dstStride, bool reluOnly, cudaStream_t st);
     opb200_status launchMaxPool(void* dst, const void* src, int N, int C, int H, int W, int Ho, int Wo, int k,
                                 int stride, int srcStride, int dstStride, cudaStream_t st);
     opb200_status launchNhwcToNchw(float* dst, const void* src, int N, int C, int H, int W, int srcStride, int dstC,

@@ -977,10 +977,15 @@ namespace opb
                 break;
             case OP_CONV: s = launchConv(op.cp, op.bnEff, net.gridCap, st); break;
             case OP_FIRSTCONV:
+            {
+                bool reluOnly = true;
+                for (float sl : op.hostSlope)
+                    reluOnly = reluOnly && sl == 0.f;
                 s = launchFirstConv(viewPtr(op.out), net.dInput, reinterpret_cast<const uint32_t*>(op.dW), op.dBias,
                                     op.dSlope, net.N, op.inC, h, w, op.k, op.pad, op.cout, net.buffers[op.out.buf].C,
-                                    st);
+                                    reluOnly, st);
                 break;
+            }
             case OP_POOL:
                 s = launchMaxPool(viewPtr(op.out), viewPtr(op.in[0]), net.N, op.in[0].C, h, w, net.lvH[op.outLevel],
                                   net.lvW[op.outLevel], op.k, op.stride, net.buffers[op.in[0].buf].C,
