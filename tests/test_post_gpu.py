@@ -195,6 +195,28 @@ def test_resize_multiscale_ragged_matches_oracle(port, cuda, sizes, ratios, targ
     assert np.array_equal(dst[0].cpu().numpy(), want)
 
 
+@pytest.mark.parametrize("guard", [64, 1])
+@pytest.mark.parametrize("sizes,ratios,target,planes", [
+    ([(46, 82)], None, (368, 656), 3),                                  # x8 streaming kernel (aligned) / band kernel
+    ([(5, 7)], None, (40, 56), 5),
+    ([(46, 82), (34, 60), (22, 40), (10, 20)], [1.0, 0.75, 0.5, 0.25], (368, 656), 2),
+    ([(5, 7), (3, 4), (1, 2)], [1.0, 0.6, 0.2], (40, 56), 5),
+])
+def test_resize_writes_only_its_target(port, cuda, sizes, ratios, target, planes, guard):
+    """out-of-bounds canary (the pool has no compute-sanitizer): the target is a window of a larger buffer whose
+    margins hold a sentinel; guard = 1 also takes the target off 16-byte alignment (the non-vectorised kernels)."""
+    rng = np.random.default_rng(5)
+    srcs = [rng.normal(0, 1, size=(1, planes, h, w)).astype(np.float32) for h, w in sizes]
+    n = planes * target[0] * target[1]
+    big = torch.full((n + 2 * guard,), -12345.0, device=cuda)
+    dst = big[guard:guard + n].view(1, planes, target[0], target[1])
+    post.resize_and_merge_gpu(dst, [torch.from_numpy(s).to(cuda) for s in srcs], ratios)
+    torch.cuda.synchronize()
+    assert bool((big[:guard] == -12345.0).all()) and bool((big[guard + n:] == -12345.0).all())
+    want = port.resize_merge([s[0] for s in srcs], target[0], target[1], ratios)
+    assert np.array_equal(dst[0].cpu().numpy(), want)
+
+
 def test_resize_errors_and_copy(cuda):
     src = torch.randn((1, 3, 10, 12), device=cuda)
     dst = torch.empty((1, 3, 10, 12), device=cuda)
