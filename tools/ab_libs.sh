@@ -8,7 +8,7 @@ for r in $(seq $rounds); do
   for lib in prev new; do
     if [ $lib = prev ]; then export OPB200_LIB_PATH=$PWD/openpose_b200/lib/libopb200_prev.so; else unset OPB200_LIB_PATH; fi
     steps=$(( b < 8 ? 200 : 40 ))
-    timeout 120 python bench.py --batch $b --steps $steps --warmup 10 --no-cpu 2>/dev/null | python -c "
+    timeout 120 python bench.py --batch $b --steps $steps --warmup 10 --no-cpu --no-engine --no-latency 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.readline()); r=d['roofline']
 print('%5d  %-4s  %8.1f  %7.3f  %7.3f  %12.1f  %s' % ($b, '$lib', d['value'], d['ms_per_step'], r['launch_ms'], r['achieved'], d['clocks']['sm_mhz']))"
