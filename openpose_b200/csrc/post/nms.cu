@@ -16,6 +16,7 @@
 #include "../common.cuh"
 #include "../net/sm100.cuh"
 #include <algorithm>
+#include <cstdlib>
 
 namespace opb
 {
@@ -127,7 +128,9 @@ namespace opb
         const float* heat; // (N, Ch, H, W)
         float thr, offx, offy;
         int parts, heatChannels, h, w, hw, maxPeaks;
-        int stages;        // ring depth; the block has stages*kNmsWarpsPerStage scanning warps + 1 producer warp
+        int stages;        // ring depth
+        int groups;        // warp groups; tile j of a block is scanned by group j % groups, out of stage j % stages
+        int warpsPerTile;  // warps of a group (each scans an equal part of the tile); groups * warpsPerTile scanning warps
         int segLen;        // pixels per scanning warp within one tile (multiple of kChunk)
         int tileRows;      // rows per tile (the staged copy adds one halo row above and below)
         int tilesPerPlane; // ceil(h / tileRows)
@@ -300,9 +303,11 @@ namespace opb
     //   * producer (1 warp, one thread): streams the tiles through a ring of `stages` shared-memory buffers with bulk
     //     async copies (tile = tileRows rows + a halo row either side, one contiguous 16-byte aligned range of the
     //     plane), so ~200 KB per SM is in flight whatever the other warps are doing;
-    //   * scanners (stages x kNmsWarpsPerStage warps): tile j of the block lives in stage j % stages and is scanned by
-    //     that stage's warps, a third each, out of shared memory -- the neighbour tests of above-threshold pixels
-    //     never wait on global memory. The only per-tile synchronisation is the stage's full/empty mbarrier pair.
+    //   * scanners (24 warps in `groups` groups of `warpsPerTile`): tile j of the block lives in ring stage j % stages and
+    //     is scanned by group j % groups, an equal part per warp, out of shared memory -- the neighbour tests of
+    //     above-threshold pixels never wait on global memory. 8 stages and 4 groups of 6: while a group scans a tile
+    //     its next one is already loaded or loading. The only per-tile synchronisation is the stage's full/empty
+    //     mbarrier pair.
     //     A warp appends its peaks to its own list and records one (start, count) group per tile;
     //   * merger (1 warp): when every scanner has left a band (the part of a channel instance inside this block) it
     //     concatenates the groups in (tile, warp) = raster order, then outputs the band: a channel held by one block
@@ -312,12 +317,12 @@ namespace opb
     __global__ void __launch_bounds__((kNmsMaxWarps + 2) * 32) nmsKernel(const NmsArgs a)
     {
         extern __shared__ __align__(128) int smem[];   // warp lists | band list | ring of tiles
-        const int S = a.stages, W = S * kNmsWarpsPerStage;
+        const int S = a.stages, NG = a.groups, WPT = a.warpsPerTile, W = NG * WPT;
         int* warpLists = smem;                                   // [2][W][maxPeaks]
         int* bandLists = smem + 2 * W * a.maxPeaks;              // [kNmsFlushBands][maxPeaks]
         // per (tile of the band, scanning warp of the tile): (first entry in the warp's list) << 16 | entries
-        int* groupInfo = bandLists + kNmsFlushBands * a.maxPeaks; // [2][tilesPerPlane * kNmsWarpsPerStage]
-        const int maxGroups = a.tilesPerPlane * kNmsWarpsPerStage;
+        int* groupInfo = bandLists + kNmsFlushBands * a.maxPeaks; // [2][tilesPerPlane * WPT]
+        const int maxGroups = a.tilesPerPlane * WPT;
         float* ring = reinterpret_cast<float*>(smem + (((2 * W + kNmsFlushBands) * a.maxPeaks + 2 * maxGroups + 3) & ~3));
         __shared__ int slotCi[kNmsFlushBands], slotCnt[kNmsFlushBands], slotBands[kNmsFlushBands];
         __shared__ int slotOwned[kNmsFlushBands], slotN[kNmsFlushBands];
@@ -339,7 +344,7 @@ namespace opb
             for (int s = 0; s < S; s++)
             {
                 sm100::mbarInit(&fullBar[s], 1);
-                sm100::mbarInit(&emptyBar[s], kNmsWarpsPerStage);
+                sm100::mbarInit(&emptyBar[s], WPT);
             }
             for (int p = 0; p < 2; p++)
             {
@@ -467,7 +472,7 @@ namespace opb
                 const int* groups = groupInfo + par * maxGroups;
                 const long long planeFirst = (long long)ci * a.tilesPerPlane;
                 const long long ga = max(g0, planeFirst), gb = min(g1, planeFirst + a.tilesPerPlane);
-                const int nGroups = (int)(gb - ga) * kNmsWarpsPerStage;
+                const int nGroups = (int)(gb - ga) * WPT;
                 sm100::mbarWait(&doneBar[par], (bandIdx >> 1) & 1);      // every scanning warp finished this band
                 // Concatenate the groups in (tile, warp) = raster order: exclusive prefix of the group sizes, then
                 // each non-empty group that starts below maxPeaks is copied to its place (<= maxPeaks copies).
@@ -488,8 +493,8 @@ namespace opb
                     const int dst = bandCount + incl - cnt;
                     if (cnt > 0 && dst < a.maxPeaks)
                     {
-                        const int tl = gi / kNmsWarpsPerStage, sub = gi - tl * kNmsWarpsPerStage;
-                        const int wq = (int)((ga - g0 + tl) % S) * kNmsWarpsPerStage + sub;
+                        const int tl = gi / WPT, sub = gi - tl * WPT;
+                        const int wq = (int)((ga - g0 + tl) % NG) * WPT + sub;
                         const int* src = lists + wq * a.maxPeaks + (info >> 16);
                         const int n = min(cnt, a.maxPeaks - dst);
                         for (int i = 0; i < n; i++)
@@ -512,10 +517,8 @@ namespace opb
         }
 
         // ---- scanning warps: nothing but scanning; a warp runs ahead of the others by up to two bands ----
-        const int stage = warp / kNmsWarpsPerStage, sub = warp - stage * kNmsWarpsPerStage;
+        const int grp = warp / WPT, sub = warp - grp * WPT;
         const float invW = 1.0f / (float)a.w;
-        const float* myTile = ring + (size_t)stage * tileFloats;
-        int round = 0;                                   // tiles this warp has consumed
         int bandIdx = 0;
         for (int ci = ciFirst; ci <= ciLast; ++ci, ++bandIdx)
         {
@@ -527,19 +530,20 @@ namespace opb
             int* groups = groupInfo + par * maxGroups;
             if (bandIdx >= 2)
                 sm100::mbarWait(&freeBar[par], ((bandIdx >> 1) - 1) & 1);   // band - 2 has been merged
-            // this warp's tiles of the band: j = g - g0 with j % S == stage
-            long long g = ga + ((stage - (int)((ga - g0) % S)) + S) % S;
+            // this warp's tiles of the band: j = g - g0 with j % NG == grp; tile j sits in ring stage j % S (its (j / S)-th use)
+            long long g = ga + ((grp - (int)((ga - g0) % NG)) + NG) % NG;
             int count = 0;
-            for (; g < gb; g += S, ++round)
+            for (; g < gb; g += NG)
             {
+                const int j = (int)(g - g0), stage = j % S;
                 const int tp = (int)(g - planeFirst);
                 const int r0 = tp * a.tileRows, r1 = min(a.h, r0 + a.tileRows);
                 const int segBegin = r0 * a.w + sub * a.segLen, segEnd = min(segBegin + a.segLen, r1 * a.w);
                 const int before = min(count, a.maxPeaks);
                 if (VEC)
                 {
-                    sm100::mbarWait(&fullBar[stage], round & 1);
-                    const float* scan = myTile - max(0, r0 - 1) * a.w;
+                    sm100::mbarWait(&fullBar[stage], (j / S) & 1);
+                    const float* scan = ring + (size_t)stage * tileFloats - max(0, r0 - 1) * a.w;
                     count = scanPixels<MODE, VEC>(a, scan, segBegin, segEnd, myList, count, lane, invW);
                     __syncwarp();
                     if (lane == 0)
@@ -548,7 +552,7 @@ namespace opb
                 else
                     count = scanPixels<MODE, VEC>(a, plane, segBegin, segEnd, myList, count, lane, invW);
                 if (lane == 0)
-                    groups[(int)(g - ga) * kNmsWarpsPerStage + sub] = (before << 16) | (min(count, a.maxPeaks) - before);
+                    groups[(int)(g - ga) * WPT + sub] = (before << 16) | (min(count, a.maxPeaks) - before);
             }
             __syncwarp();
             if (lane == 0)
@@ -592,8 +596,20 @@ extern "C" opb200_status opb200_nms(float* peaks, void* scratch, const float* he
     // Shared memory: warp lists (two sets), band list, the group table of a whole plane, then the ring.
     // Ring geometry: 8 stages of 8-row tiles when they fit; wider rows get shorter tiles, then fewer stages.
     // The unstaged mode (rows not 16-byte aligned: warps scan global memory) keeps the same tiling without a ring.
+    // Scanning warps: 3 per ring stage. With the full ring of 8 stages and tiles large enough the 24 warps form 4 groups of
+    // 6 instead of 8 groups of 3: a group then always has its next tile loaded (or loading) while it scans, whereas a
+    // group tied to one stage waits out the whole load of its next tile -- on maps where most tiles take the candidate
+    // path (crowds, the noise of a random-weight net) the warps spent 37 % of their time in that wait.
+    auto warpsPerTileFor = [&](int st, int rows) {
+        // (the group count must divide the stage count: a stage is then always consumed by the same group, which waits for
+        // tile j + stages only after it has consumed tile j -- with a rotating assignment a group could poll the stage's
+        // barrier a whole phase early and the one parity bit would alias; 3 groups of 8 over 8 stages deadlocked)
+        constexpr int wide = 2 * kNmsWarpsPerStage;
+        static_assert(kNmsMaxStages % (kNmsMaxWarps / wide) == 0, "group count must divide the stage count");
+        return (st == kNmsMaxStages && (long long)rows * w >= (long long)wide * 2 * kChunk) ? wide : kNmsWarpsPerStage;
+    };
     auto listBytesFor = [&](int st, int rows) {
-        const size_t groups = (size_t)((h + rows - 1) / rows) * kNmsWarpsPerStage;
+        const size_t groups = (size_t)((h + rows - 1) / rows) * warpsPerTileFor(st, rows);
         return sizeof(int) * ((((size_t)st * kNmsWarpsPerStage * 2 + kNmsFlushBands) * maxPeaks + 2 * groups + 3) & ~(size_t)3);
     };
     int stages = 0, tileRows = 0;
@@ -614,7 +630,9 @@ extern "C" opb200_status opb200_nms(float* peaks, void* scratch, const float* he
     a.stages = stages;
     a.tileRows = tileRows;
     a.tilesPerPlane = (h + tileRows - 1) / tileRows;
-    a.segLen = ((tileRows * w + kNmsWarpsPerStage - 1) / kNmsWarpsPerStage + kChunk - 1) / kChunk * kChunk;
+    a.warpsPerTile = warpsPerTileFor(stages, tileRows);
+    a.groups = stages * kNmsWarpsPerStage / a.warpsPerTile;
+    a.segLen = ((tileRows * w + a.warpsPerTile - 1) / a.warpsPerTile + kChunk - 1) / kChunk * kChunk;
     a.tiles = (long long)ci * a.tilesPerPlane;
     // one block per SM; a channel may be cut into at most kNmsMaxBands bands
     long long gridLL = std::min<long long>(a.tiles, kNumSMsB200);
