@@ -42,12 +42,12 @@ namespace opb
         int storeBf16;                        // 0: skip the bf16 NHWC store (nobody reads it)
         int poolFused;                        // 1: 2x2/2 MAX pooling in the epilogue; oMap is the pooled blob, box (32, 4, 8, 1)
         int actMode;                          // 1: every slope is 0 (ReLU: add + max); 0: general per-channel slope
-        // Frame-interleaved ("flat") levels: memory [y][n][x of flatPitch = W + 1][c] with a zero separator column after
-        // every frame, so the batch is ONE image of width N * (W + 1) whose 8-pixel groups run across frame borders (no
+        // Frame-interleaved ("flat") levels: memory [y][n][x of flatPitch = W + sep][c] with sep zero separator columns
+        // (the widest horizontal padding of the level's convs: 1 for 3x3, 3 for 7x7) after every frame, so the batch is ONE image of width N * (W + sep) whose 8-pixel groups run across frame borders (no
         // per-frame rounding of W up to 8) and whose separators are the horizontal zero padding. The kernel then sees
         // N = 1, W = N * flatPitch, and its epilogue writes zeros into the separator columns; only the pooled store of the
         // level above goes through a per-frame map (C, W, N, H), which clips at each frame's right edge.
-        int flatPitch;                        // 0: plain [n][y][x][c]; else W + 1 of the real frames
+        int flatPitch;                        // 0: plain [n][y][x][c]; else W + sep of the real frames
         int flatW, flatN;                     // real frame width and count (fp32 NCHW output addressing)
         int poolOutFlat;                      // the pooled blob's level is flat: pooled store coordinates are (c, x, n, y)
         int reverse;                          // 1: M-tile groups are walked last to first (serpentine order across layers: the

@@ -452,7 +452,7 @@ namespace opb
                         tmemBase + (acc * 2 + j) * Cfg::kAccStride + ((uint32_t)(quad * 32) << 16);
                     const int x = tc.x0 + tw, y = tc.y0 + th;
                     const bool inImage = (x < p.W) && (y < p.H);
-                    const bool isSeparator = p.flatPitch != 0 && (x % p.flatPitch) == p.flatW;
+                    const bool isSeparator = p.flatPitch != 0 && (x % p.flatPitch) >= p.flatW;
 #pragma unroll 1
                     for (int q = half; q < kPieces && !(kConvDebug && (p.debugMode & 1)); q += 2)
                     {

@@ -188,7 +188,8 @@ namespace opb
         // shape-dependent state
         int N = 0, H = 0, W = 0;
         std::vector<int> lvH, lvW;
-        std::vector<int> lvFlat;   // per level: 1 = frame-interleaved layout [y][n][x of W + 1][c] (conv_params.h)
+        std::vector<int> lvFlat;   // per level: 1 = frame-interleaved layout [y][n][x of W + sep][c] (conv_params.h)
+        std::vector<int> lvSep;    // zero separator columns after every frame of a flat level = the widest horizontal padding of its convs
         uint8_t* arena = nullptr;
         size_t arenaBytes = 0;
         float* dInput = nullptr;
@@ -763,11 +764,21 @@ namespace opb
         // (TMA loads, TMA stores, fused pooled stores) or the fp32 converter, and where it saves M tiles.
         const bool flatEnabled = !(std::getenv("OPB200_CONV_FLAT") && std::atoi(std::getenv("OPB200_CONV_FLAT")) == 0);
         net.lvFlat.assign(net.levels.size(), 0);
+        net.lvSep.assign(net.levels.size(), 1);
         for (size_t l = 0; l < net.levels.size(); ++l)
         {
             const int w = net.lvW[l], h = net.lvH[l];
+            // The separator columns are the horizontal zero padding between neighbouring frames, so there must be as many
+            // as the widest padding of the level's convs: 1 for 3x3, 3 for the 7x7 layers of COCO / hand / face. (Round 1
+            // and most of round 2 always used one: with pad 3 a 7x7 filter then read two columns of the NEIGHBOURING frame
+            // -- wrong outputs for those graphs whenever the batch was large enough for the flat layout to be chosen.)
+            int sep = 1;
+            for (const auto& op : net.ops)
+                if (op.kind == OP_CONV && op.level == (int)l && op.pad > sep)
+                    sep = op.pad;
+            net.lvSep[l] = sep;
             const long long tilesPlain = (long long)N * ((w + kConvTileW - 1) / kConvTileW);
-            const long long tilesFlat = ((long long)N * (w + 1) + kConvTileW - 1) / kConvTileW;
+            const long long tilesFlat = ((long long)N * (w + sep) + kConvTileW - 1) / kConvTileW;
             bool ok = flatEnabled && N > 1 && tilesFlat < tilesPlain && h > 0;
             for (const auto& op : net.ops)
             {
@@ -786,7 +797,7 @@ namespace opb
         }
         for (auto& b : net.buffers)
         {
-            const int w = net.lvW[b.level] + (net.lvFlat[b.level] ? 1 : 0);
+            const int w = net.lvW[b.level] + (net.lvFlat[b.level] ? net.lvSep[b.level] : 0);
             b.offset = carve((size_t)N * net.lvH[b.level] * w * b.C * 2);
         }
         net.inputBytes = (size_t)N * net.inputC * H * W * 4;
@@ -827,8 +838,9 @@ namespace opb
             std::memset(&p, 0, sizeof(p));
             p.reverse = (serpentine && (convIndex++ & 1) == 0) ? 1 : 0;   // the first-layer kernel runs first to last
             const bool flat = net.lvFlat[op.level] != 0;
-            const int kw = flat ? N * (w + 1) : w, kn = flat ? 1 : N;   // the image the kernel sees
-            p.flatPitch = flat ? w + 1 : 0;
+            const int sep = net.lvSep[op.level];
+            const int kw = flat ? N * (w + sep) : w, kn = flat ? 1 : N;   // the image the kernel sees
+            p.flatPitch = flat ? w + sep : 0;
             p.flatW = w;
             p.flatN = N;
             p.tilesX = (kw + kConvTileW - 1) / kConvTileW;
@@ -934,13 +946,13 @@ namespace opb
             p.poolOutFlat = (op.poolFused && net.lvFlat[op.poolLevel]) ? 1 : 0;
             if (op.poolFused && p.poolOutFlat)   // pooled blob on a flat level: per-frame store map
                 st = makeFlatStoreMap(&p.oMap, viewPtr(op.poolOut), op.poolOut.C, net.lvW[op.poolLevel],
-                                      net.lvH[op.poolLevel], N, net.lvW[op.poolLevel] + 1,
+                                      net.lvH[op.poolLevel], N, net.lvW[op.poolLevel] + net.lvSep[op.poolLevel],
                                       net.buffers[op.poolOut.buf].C, 32, kConvTileW / 2, kConvTileH / 2);
             else if (op.poolFused)   // the pooled blob, one (32 ch, 4, 8) box per tile
                 st = makeActivationMap(&p.oMap, viewPtr(op.poolOut), op.poolOut.C, net.lvW[op.poolLevel],
                                        net.lvH[op.poolLevel], N, net.buffers[op.poolOut.buf].C, 32, kConvTileW / 2,
                                        kConvTileH / 2, false);
-            else   // (flat level: one image of width N * (W + 1); the epilogue writes zeros into the separator columns)
+            else   // (flat level: one image of width N * (W + sep); the epilogue writes zeros into the separator columns)
                 st = makeActivationMap(&p.oMap, viewPtr(op.out), op.out.C, kw, h, kn, net.buffers[op.out.buf].C, 32,
                                        kConvTileW, kConvTileH, false);
             if (st != OPB200_OK)
@@ -995,8 +1007,9 @@ namespace opb
             {
                 const long long sc = net.buffers[op.in[0].buf].C;
                 const bool flat = net.lvFlat[op.level] != 0;
+                const int pitch = w + net.lvSep[op.level];
                 s = launchNhwcToNchw(net.dOut32, viewPtr(op.in[0]), net.N, op.in[0].C, h, w, (int)sc, net.outC,
-                                     op.out32Off, st, flat ? (w + 1) * sc : 0, flat ? (long long)net.N * (w + 1) * sc : 0);
+                                     op.out32Off, st, flat ? pitch * sc : 0, flat ? (long long)net.N * pitch * sc : 0);
             }
                 break;
             }
@@ -1257,9 +1270,10 @@ extern "C" opb200_status opb200_net_read_blob(opb200_net* n, const char* name, f
     {
         const long long sc = net.buffers[v.buf].C;
         const bool flat = net.lvFlat[b.level] != 0;
+        const int pitch = w + net.lvSep[b.level];
         s = launchNhwcToNchw(tmp, net.arena + net.buffers[v.buf].offset + (size_t)v.cOff * 2, net.N, v.C, h, w,
-                             (int)sc, b.C, cOff, nullptr, flat ? (w + 1) * sc : 0,
-                             flat ? (long long)net.N * (w + 1) * sc : 0);
+                             (int)sc, b.C, cOff, nullptr, flat ? pitch * sc : 0,
+                             flat ? (long long)net.N * pitch * sc : 0);
         if (s != OPB200_OK)
             break;
         cOff += v.C;

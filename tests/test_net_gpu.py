@@ -130,6 +130,36 @@ def test_openpose_models_within_tolerance(cuda, model, shape):
     net.close()
 
 
+@pytest.mark.parametrize("model,hw,batches", [("hand", (96, 96), (1, 3, 8)), ("face", (96, 96), (1, 4)),
+                                              ("coco", (64, 96), (1, 5)), ("body_25", (64, 96), (1, 5)),
+                                              ("hand", (368, 368), (1, 8))])
+def test_output_of_a_frame_does_not_depend_on_its_batch(cuda, model, hw, batches):
+    """Frames are independent: frame 0 has the same output bits whatever batch it is run in, and stays within tolerance
+    of the oracle. (Regression: the frame-interleaved layout used ONE zero separator column between frames, enough for
+    the padding of a 3x3 but not of the 7x7 layers of COCO / hand / face, whose filters then read the neighbouring
+    frame as soon as the batch was large enough for that layout to be chosen.)"""
+    h, w = hw
+    proto, cm, ref = ref_net.build(model, 4321)
+    x0 = synth.frames_to_net_input(synth.frames(1, h, w, 7))
+    torch.set_num_threads(os.cpu_count() or 1)
+    want = ref.forward(x0, keep=["net_output"])["net_output"][0]
+    rms = float(np.sqrt((want ** 2).mean()))
+    net = NetB200(proto, cm)
+    net.initializationOnThread()
+    first = None
+    for n in batches:
+        x = np.concatenate([x0, synth.frames_to_net_input(synth.frames(n - 1, h, w, 9))]) if n > 1 else x0
+        net.forwardPass(torch.from_numpy(np.ascontiguousarray(x)).to(cuda))
+        got = net.getOutputBlobArray().cpu().numpy()[0].copy()
+        err = float(np.abs(got - want).max())
+        print("%s %s batch %d: max-abs vs fp32 oracle %.4g (rms %.4g)" % (model, hw, n, err, rms))
+        assert err <= TOL_NET and err <= REL_FP32 * rms, (n, err, rms)
+        if first is None:
+            first = got
+        assert np.array_equal(got, first), "frame 0 differs between batch %d and batch %d" % (batches[0], n)
+    net.close()
+
+
 def test_flat_level_layout_is_bit_identical(cuda, monkeypatch):
     """Frame-interleaved levels (conv_params.h: tiles run across frame borders, zero separator columns) change which
     tile computes a pixel, not its arithmetic: outputs and intermediate blobs equal the plain layout bit for bit."""
