@@ -326,6 +326,35 @@ opb200_status opb200_engine_next(opb200_engine* engine, unsigned long long* firs
                                  float* keypoints, float* scores, int* counts);
 int opb200_engine_in_flight(opb200_engine* engine);   /* batches submitted and not yet returned by next */
 
+/* ---------------------------------------------------------------------------------------------------
+ * Multi-GPU hand / face crop engine: the same worker topology for the keypoint nets that run on per-person crops
+ * (BASELINE config 4: "per-person crops sharded across GPUs"). A batch = ONE u8 BGR frame + the 2x3 double inverse maps
+ * (crop pixel -> frame position, what opb200_crop_warp takes) of up to `batch` crops of it: both hands of every person,
+ * or every face. Per batch: H2D, opb200_crop_warp into the net's input buffer, opb200_net_forward, opb200_resize_merge
+ * (x8), opb200_maximum, D2H -- the device part of HandExtractorCaffe::forwardPass / FaceExtractorCaffe::forwardPass
+ * (reference: src/openpose/hand/handExtractorCaffe.cpp:305-464, src/openpose/face/faceExtractorCaffe.cpp:175-300) for all
+ * crops of the batch at once. Batches go round the devices, results come back in submission order:
+ *   submit(frame_id, frame, matrices, n)  (or opb200_engine_acquire: staging = frame bytes, then the matrices at
+ *                                          opb200_crop_engine_matrix_offset(); opb200_engine_commit(frame_id, n));
+ *   next -> peaks (n, heat_channels - 1, 3) = (x, y, value) of every part's maximum in CROP coordinates; the caller maps
+ *           them back through its affine exactly as the reference does after maximumGpu.
+ * Created with opb200_crop_engine_create, destroyed with opb200_engine_destroy; opb200_engine_in_flight applies.
+ * ------------------------------------------------------------------------------------------------- */
+typedef struct opb200_crop_engine_config
+{
+    int heat_channels;              /* channels of the net's output incl. background: 22 (hand), 71 (face) */
+    int net_side;                   /* crop / net input side, a multiple of 8 (368) */
+    int frame_w, frame_h;           /* resolution of the u8 BGR frames */
+    int batch;                      /* crops per batch (per device) */
+    int lanes;                      /* batches in flight per device, 1..8 */
+} opb200_crop_engine_config;
+opb200_status opb200_crop_engine_create(opb200_engine** out, const char* prototxt, const char* caffemodel,
+                                        const int* gpu_ids, int n_gpus, const opb200_crop_engine_config* cfg);
+size_t opb200_crop_engine_matrix_offset(opb200_engine* engine);   /* byte offset of the matrices in a staging buffer */
+opb200_status opb200_crop_engine_submit(opb200_engine* engine, unsigned long long frame_id, const unsigned char* frame,
+                                        const double* matrices, int n_crops);
+opb200_status opb200_crop_engine_next(opb200_engine* engine, unsigned long long* frame_id, int* n_crops, float* peaks);
+
 #ifdef __cplusplus
 }
 #endif

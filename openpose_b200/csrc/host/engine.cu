@@ -59,7 +59,7 @@ namespace
         opb200_net* net = nullptr;
         cudaStream_t compute = nullptr, copy = nullptr;
         float *dHeat = nullptr, *dPeaks = nullptr;
-        void *nmsScratch = nullptr, *connectScratch = nullptr;
+        void *nmsScratch = nullptr, *connectScratch = nullptr, *maxScratch = nullptr;
         std::vector<Lane> lanes;
         std::deque<int> pending, issued;
         std::thread worker;
@@ -69,8 +69,11 @@ namespace
 struct opb200_engine
 {
     opb200_engine_config cfg;
+    bool cropMode = false;                    // hand / face crops of one frame per batch (opb200_crop_engine_create)
+    opb200_crop_engine_config crop;
     int parts = 0, channels = 0;
-    size_t frameBytes = 0, kpFloats = 0;
+    size_t frameBytes = 0, kpFloats = 0;      // bytes of one staged input unit; result floats per frame (per crop)
+    size_t stagingBytes = 0, matOffset = 0;   // crop mode: frame | 2x3 double matrices of up to `batch` crops
     std::vector<std::unique_ptr<Device>> devices;
     std::mutex mtx;
     std::condition_variable cv;
@@ -84,8 +87,58 @@ struct opb200_engine
 namespace
 {
     // everything one batch needs, enqueued without a host synchronisation
+    // crop mode: one u8 frame + the affine maps of ln.n crops -> opb200_crop_warp (into the net's input buffer) ->
+    // opb200_net_forward -> opb200_resize_merge (x8) -> opb200_maximum -> D2H of (n, parts, 3) peaks in crop coordinates:
+    // the device part of HandExtractorCaffe::forwardPass / FaceExtractorCaffe::forwardPass for all crops of the batch
+    // at once (reference: src/openpose/hand/handExtractorCaffe.cpp:305-464, src/openpose/face/faceExtractorCaffe.cpp:175-300)
+    opb200_status issueCropBatch(opb200_engine* e, Device& d, Lane& ln)
+    {
+        const opb200_crop_engine_config& c = e->crop;
+        const int n = ln.n;
+        OPB_CUDA(cudaMemcpyAsync(ln.dIn, ln.hIn, e->stagingBytes, cudaMemcpyHostToDevice, d.copy));
+        OPB_CUDA(cudaEventRecord(ln.h2d, d.copy));
+        OPB_CUDA(cudaStreamWaitEvent(d.compute, ln.h2d, 0));
+        // the net always runs at the full batch shape (one CUDA graph, no re-planning when the number of crops changes from
+        // frame to frame); slots beyond n keep whatever an earlier batch left there and their outputs are ignored
+        const int inShape[4] = {c.batch, 3, c.net_side, c.net_side};
+        float* netIn = nullptr;
+        opb200_status s = opb200_net_input_buffer(d.net, inShape, &netIn, d.compute);
+        if (s != OPB200_OK)
+            return s;
+        s = opb200_crop_warp(netIn, ln.dIn, reinterpret_cast<const double*>(ln.dIn + e->matOffset), n, c.frame_h, c.frame_w,
+                             c.net_side, c.net_side, d.compute);
+        if (s != OPB200_OK)
+            return s;
+        s = opb200_net_forward(d.net, netIn, 1, inShape, d.compute);
+        if (s != OPB200_OK)
+            return s;
+        const float* netOut = nullptr;
+        int outShape[4];
+        s = opb200_net_output(d.net, &netOut, outShape);
+        if (s != OPB200_OK)
+            return s;
+        OPB_REQUIRE(outShape[1] == c.heat_channels && outShape[2] * 8 == c.net_side && outShape[3] * 8 == c.net_side,
+                    "crop engine: the net's output is not (heat_channels, net_side / 8, net_side / 8)");
+        const int heatShape[4] = {n, c.heat_channels, c.net_side, c.net_side};
+        const int peakShape[4] = {n, 1, c.heat_channels - 1, 3};
+        const float* srcs[1] = {netOut};
+        const int srcShapes[1][4] = {{n, outShape[1], outShape[2], outShape[3]}};
+        const float ratios[1] = {1.f};
+        s = opb200_resize_merge(d.dHeat, srcs, srcShapes, ratios, 1, heatShape, d.compute);
+        if (s != OPB200_OK)
+            return s;
+        s = opb200_maximum(ln.dKp, d.maxScratch, d.dHeat, peakShape, heatShape, d.compute);
+        if (s != OPB200_OK)
+            return s;
+        OPB_CUDA(cudaMemcpyAsync(ln.hKp, ln.dKp, sizeof(float) * e->kpFloats * n, cudaMemcpyDeviceToHost, d.compute));
+        OPB_CUDA(cudaEventRecord(ln.done, d.compute));
+        return OPB200_OK;
+    }
+
     opb200_status issueBatch(opb200_engine* e, Device& d, Lane& ln)
     {
+        if (e->cropMode)
+            return issueCropBatch(e, d, ln);
         const opb200_engine_config& c = e->cfg;
         const int B = ln.n;
         OPB_CUDA(cudaMemcpyAsync(ln.dIn, ln.hIn, e->frameBytes * B, cudaMemcpyHostToDevice, d.copy));
@@ -220,6 +273,7 @@ namespace
         cudaFree(d.dPeaks);
         cudaFree(d.nmsScratch);
         cudaFree(d.connectScratch);
+        cudaFree(d.maxScratch);
         if (d.net)
             opb200_net_destroy(d.net);
         if (d.compute)
@@ -237,6 +291,35 @@ namespace
             return s;
         OPB_CUDA(cudaStreamCreateWithFlags(&d.compute, cudaStreamNonBlocking));
         OPB_CUDA(cudaStreamCreateWithFlags(&d.copy, cudaStreamNonBlocking));
+        if (e->cropMode)
+        {
+            const opb200_crop_engine_config& cc = e->crop;
+            const size_t n = (size_t)cc.batch;
+            const int heatShape[4] = {cc.batch, cc.heat_channels, cc.net_side, cc.net_side};
+            const int peakShape[4] = {cc.batch, 1, cc.heat_channels - 1, 3};
+            OPB_CUDA(cudaMalloc(&d.dHeat, sizeof(float) * n * cc.heat_channels * cc.net_side * cc.net_side));
+            OPB_CUDA(cudaMalloc(&d.maxScratch, opb200_maximum_scratch_bytes(peakShape, heatShape)));
+            {
+                const int inShape[4] = {cc.batch, 3, cc.net_side, cc.net_side};
+                float* netIn = nullptr;
+                const opb200_status si = opb200_net_input_buffer(d.net, inShape, &netIn, d.compute);
+                if (si != OPB200_OK)
+                    return si;
+                OPB_CUDA(cudaMemsetAsync(netIn, 0, sizeof(float) * n * 3 * cc.net_side * cc.net_side, d.compute));
+                OPB_CUDA(cudaStreamSynchronize(d.compute));
+            }
+            d.lanes.resize(cc.lanes);
+            for (auto& ln : d.lanes)
+            {
+                OPB_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&ln.hIn), e->stagingBytes, cudaHostAllocDefault));
+                OPB_CUDA(cudaMalloc(&ln.dIn, e->stagingBytes));
+                OPB_CUDA(cudaMalloc(&ln.dKp, sizeof(float) * e->kpFloats * n));
+                OPB_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&ln.hKp), sizeof(float) * e->kpFloats * n, cudaHostAllocDefault));
+                OPB_CUDA(cudaEventCreateWithFlags(&ln.h2d, cudaEventDisableTiming));
+                OPB_CUDA(cudaEventCreateWithFlags(&ln.done, cudaEventDisableTiming));
+            }
+            return OPB200_OK;
+        }
         const size_t B = (size_t)c.batch;
         const int heatShape[4] = {c.batch, e->channels, c.net_h, c.net_w};
         const int peaksShape[4] = {c.batch, e->parts, c.connect.max_peaks + 1, 3};
@@ -300,6 +383,48 @@ extern "C" opb200_status opb200_engine_create(opb200_engine** out, const char* p
     *out = e.release();
     return OPB200_OK;
 }
+
+extern "C" opb200_status opb200_crop_engine_create(opb200_engine** out, const char* prototxt, const char* caffemodel,
+                                                   const int* gpu_ids, int n_gpus, const opb200_crop_engine_config* cfg)
+{
+    OPB_REQUIRE(out && prototxt && caffemodel && gpu_ids && cfg, "crop_engine_create: null argument");
+    *out = nullptr;
+    OPB_REQUIRE(n_gpus >= 1 && n_gpus <= 64, "crop_engine_create: between 1 and 64 devices");
+    OPB_REQUIRE(cfg->batch >= 1 && cfg->lanes >= 1 && cfg->lanes <= 8, "crop_engine_create: bad batch / lanes");
+    OPB_REQUIRE(cfg->heat_channels >= 2, "crop_engine_create: heat_channels counts the background channel too (22 hand, 71 face)");
+    OPB_REQUIRE(cfg->net_side > 0 && cfg->net_side % 8 == 0, "crop_engine_create: the net side must be a positive multiple of 8");
+    OPB_REQUIRE(cfg->frame_w > 0 && cfg->frame_h > 0, "crop_engine_create: bad frame size");
+    std::unique_ptr<opb200_engine> e(new opb200_engine());
+    e->cropMode = true;
+    e->crop = *cfg;
+    e->cfg = opb200_engine_config();
+    e->cfg.batch = cfg->batch;
+    e->cfg.lanes = cfg->lanes;
+    e->parts = cfg->heat_channels - 1;
+    e->channels = cfg->heat_channels;
+    e->frameBytes = (size_t)cfg->frame_h * cfg->frame_w * 3;
+    e->matOffset = (e->frameBytes + 15) & ~(size_t)15;
+    e->stagingBytes = e->matOffset + sizeof(double) * 6 * (size_t)cfg->batch;
+    e->kpFloats = (size_t)e->parts * 3;
+    for (int i = 0; i < n_gpus; ++i)
+    {
+        e->devices.emplace_back(new Device());
+        e->devices.back()->gpu = gpu_ids[i];
+        const opb200_status s = createDevice(e.get(), *e->devices.back(), prototxt, caffemodel);
+        if (s != OPB200_OK)
+        {
+            for (auto& d : e->devices)
+                destroyDevice(*d);
+            return s;
+        }
+    }
+    for (auto& d : e->devices)
+        d->worker = std::thread(workerLoop, e.get(), d.get());
+    *out = e.release();
+    return OPB200_OK;
+}
+
+extern "C" size_t opb200_crop_engine_matrix_offset(opb200_engine* e) { return (e && e->cropMode) ? e->matOffset : 0; }
 
 extern "C" void opb200_engine_destroy(opb200_engine* e)
 {
@@ -372,6 +497,7 @@ extern "C" opb200_status opb200_engine_submit(opb200_engine* e, unsigned long lo
                                               const unsigned char* frames, int n_frames)
 {
     OPB_REQUIRE(e && frames, "engine_submit: null argument");
+    OPB_REQUIRE(!e->cropMode, "engine_submit: a crop engine takes opb200_crop_engine_submit");
     OPB_REQUIRE(n_frames >= 1 && n_frames <= e->cfg.batch, "engine_submit: between 1 and `batch` frames");
     unsigned char* staging = nullptr;
     const opb200_status s = opb200_engine_acquire(e, &staging);
@@ -393,6 +519,7 @@ extern "C" opb200_status opb200_engine_next(opb200_engine* e, unsigned long long
                                             float* keypoints, float* scores, int* counts)
 {
     OPB_REQUIRE(e && first_frame_id && n_frames && keypoints && scores && counts, "engine_next: null argument");
+    OPB_REQUIRE(!e->cropMode, "engine_next: a crop engine takes opb200_crop_engine_next");
     std::unique_lock<std::mutex> lock(e->mtx);
     OPB_REQUIRE(!e->order.empty(), "engine_next: nothing was submitted");
     const std::pair<int, int> head = e->order.front();
@@ -410,6 +537,46 @@ extern "C" opb200_status opb200_engine_next(opb200_engine* e, unsigned long long
     std::memcpy(keypoints, ln.hKp, sizeof(float) * e->kpFloats * B);
     std::memcpy(scores, ln.hSc, sizeof(float) * e->cfg.capacity * B);
     std::memcpy(counts, ln.hCnt, sizeof(int) * B);
+    lock.lock();
+    ln.state = LANE_FREE;
+    e->order.pop_front();
+    e->cv.notify_all();
+    return OPB200_OK;
+}
+
+extern "C" opb200_status opb200_crop_engine_submit(opb200_engine* e, unsigned long long frame_id, const unsigned char* frame,
+                                                   const double* matrices, int n_crops)
+{
+    OPB_REQUIRE(e && frame && matrices, "crop_engine_submit: null argument");
+    OPB_REQUIRE(e->cropMode, "crop_engine_submit: not a crop engine");
+    OPB_REQUIRE(n_crops >= 1 && n_crops <= e->crop.batch, "crop_engine_submit: between 1 and `batch` crops");
+    unsigned char* staging = nullptr;
+    const opb200_status s = opb200_engine_acquire(e, &staging);
+    if (s != OPB200_OK)
+        return s;
+    std::memcpy(staging, frame, e->frameBytes);
+    std::memcpy(staging + e->matOffset, matrices, sizeof(double) * 6 * (size_t)n_crops);
+    return opb200_engine_commit(e, frame_id, n_crops);
+}
+
+extern "C" opb200_status opb200_crop_engine_next(opb200_engine* e, unsigned long long* frame_id, int* n_crops, float* peaks)
+{
+    OPB_REQUIRE(e && frame_id && n_crops && peaks, "crop_engine_next: null argument");
+    OPB_REQUIRE(e->cropMode, "crop_engine_next: not a crop engine");
+    std::unique_lock<std::mutex> lock(e->mtx);
+    OPB_REQUIRE(!e->order.empty(), "crop_engine_next: nothing was submitted");
+    const std::pair<int, int> head = e->order.front();
+    Lane& ln = e->devices[head.first]->lanes[head.second];
+    e->cv.wait(lock, [&] { return e->stop || ln.state == LANE_DONE; });
+    if (ln.state != LANE_DONE)
+    {
+        setError("engine: %s", e->error.empty() ? "stopped" : e->error.c_str());
+        return OPB200_ERR_CUDA;
+    }
+    *frame_id = ln.firstId;
+    *n_crops = ln.n;
+    lock.unlock();
+    std::memcpy(peaks, ln.hKp, sizeof(float) * e->kpFloats * (size_t)ln.n);
     lock.lock();
     ln.state = LANE_FREE;
     e->order.pop_front();

@@ -20,7 +20,17 @@ class EngineConfig(C.Structure):
                 ("scale_input_to_net", C.c_float), ("nms_threshold", C.c_float), ("connect", ConnectParams)]
 
 
+class CropEngineConfig(C.Structure):
+    _fields_ = [("heat_channels", C.c_int), ("net_side", C.c_int), ("frame_w", C.c_int), ("frame_h", C.c_int),
+                ("batch", C.c_int), ("lanes", C.c_int)]
+
+
 _lib.register({
+    "opb200_crop_engine_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_char_p, C.c_char_p, C.POINTER(C.c_int), C.c_int,
+                                            C.POINTER(CropEngineConfig)]),
+    "opb200_crop_engine_matrix_offset": (C.c_size_t, [C.c_void_p]),
+    "opb200_crop_engine_submit": (C.c_int, [C.c_void_p, C.c_ulonglong, C.c_void_p, C.c_void_p, C.c_int]),
+    "opb200_crop_engine_next": (C.c_int, [C.c_void_p, C.POINTER(C.c_ulonglong), C.POINTER(C.c_int), C.c_void_p]),
     "opb200_engine_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_char_p, C.c_char_p, C.POINTER(C.c_int), C.c_int,
                                        C.POINTER(EngineConfig)]),
     "opb200_engine_destroy": (None, [C.c_void_p]),
@@ -95,6 +105,53 @@ class PoseEngine:
         if copy:
             out = tuple(a.copy() for a in out)
         return (int(fid.value),) + out
+
+    def in_flight(self) -> int:
+        return int(_lib.lib().opb200_engine_in_flight(self._h))
+
+    def close(self) -> None:
+        if self._h:
+            _lib.lib().opb200_engine_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class CropEngine:
+    """Hand / face crops over one or more GPUs (C ABI: opb200_crop_engine_*): one u8 BGR frame + the 2x3 inverse affine
+    maps of its crops in, (n_crops, parts, 3) maxima in crop coordinates out, submission order kept. The device part of
+    HandExtractorCaffe::forwardPass / FaceExtractorCaffe::forwardPass (src/openpose/hand/handExtractorCaffe.cpp:305-464,
+    src/openpose/face/faceExtractorCaffe.cpp:175-300) for all crops of a batch at once."""
+
+    def __init__(self, prototxt: str, caffemodel: str, heat_channels: int, gpus: Sequence[int] = (0,),
+                 frame_size: Tuple[int, int] = (1280, 720), net_side: int = 368, batch: int = 16, lanes: int = 2):
+        self.cfg = CropEngineConfig(int(heat_channels), int(net_side), frame_size[0], frame_size[1], int(batch), int(lanes))
+        self.parts, self.batch = int(heat_channels) - 1, int(batch)
+        self.frame_shape = (frame_size[1], frame_size[0], 3)
+        L = _lib.lib()
+        ids = (C.c_int * len(gpus))(*[int(g) for g in gpus])
+        self._h = C.c_void_p()
+        _lib.check(L.opb200_crop_engine_create(C.byref(self._h), prototxt.encode(), caffemodel.encode(), ids, len(gpus),
+                                               C.byref(self.cfg)))
+        self._peaks = np.empty((batch, self.parts, 3), np.float32)
+
+    def submit(self, frame_id: int, frame: np.ndarray, matrices: np.ndarray) -> None:
+        frame = np.ascontiguousarray(frame, np.uint8)
+        matrices = np.ascontiguousarray(matrices, np.float64).reshape(-1, 2, 3)
+        if frame.shape != self.frame_shape:
+            raise Opb200Error("frame must be (%d, %d, 3) uint8" % self.frame_shape[:2])
+        _lib.check(_lib.lib().opb200_crop_engine_submit(self._h, int(frame_id), frame.ctypes.data, matrices.ctypes.data,
+                                                        matrices.shape[0]))
+
+    def next(self):
+        """(frame_id, peaks (n_crops, parts, 3)) of the oldest submitted batch."""
+        fid, n = C.c_ulonglong(), C.c_int()
+        _lib.check(_lib.lib().opb200_crop_engine_next(self._h, C.byref(fid), C.byref(n), self._peaks.ctypes.data))
+        return int(fid.value), self._peaks[:n.value].copy()
 
     def in_flight(self) -> int:
         return int(_lib.lib().opb200_engine_in_flight(self._h))
