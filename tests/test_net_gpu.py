@@ -132,7 +132,9 @@ def test_openpose_models_within_tolerance(cuda, model, shape):
 
 @pytest.mark.parametrize("model,hw,batches", [("hand", (96, 96), (1, 3, 8)), ("face", (96, 96), (1, 4)),
                                               ("coco", (64, 96), (1, 5)), ("body_25", (64, 96), (1, 5)),
-                                              ("hand", (368, 368), (1, 8))])
+                                              ("hand", (368, 368), (1, 8)), ("coco", (72, 88), (1, 6, 13)),
+                                              ("face", (120, 56), (1, 7)), ("body_25", (72, 88), (1, 11)),
+                                              ("hand", (136, 136), (1, 2, 6))])
 def test_output_of_a_frame_does_not_depend_on_its_batch(cuda, model, hw, batches):
     """Frames are independent: frame 0 has the same output bits whatever batch it is run in, and stays within tolerance
     of the oracle. (Regression: the frame-interleaved layout used ONE zero separator column between frames, enough for
