@@ -159,6 +159,14 @@ def test_output_of_a_frame_does_not_depend_on_its_batch(cuda, model, hw, batches
         if first is None:
             first = got
         assert np.array_equal(got, first), "frame 0 differs between batch %d and batch %d" % (batches[0], n)
+    # every frame of the largest batch against the oracle (the first and the last frame sit at the ends of the interleaved
+    # image, the others between two neighbours)
+    if h * w <= 96 * 96:
+        all_want = ref.forward(np.ascontiguousarray(x), keep=["net_output"])["net_output"]
+        all_got = net.getOutputBlobArray().cpu().numpy()
+        errs = np.abs(all_got - all_want).reshape(all_got.shape[0], -1).max(axis=1)
+        print("%s %s batch %d: per-frame max-abs vs fp32 oracle %s" % (model, hw, x.shape[0], np.round(errs, 4)))
+        assert float(errs.max()) <= TOL_NET and float(errs.max()) <= REL_FP32 * rms, errs
     net.close()
 
 
