@@ -23,9 +23,9 @@ def _reference_chain(proto, cm, frames, eng, cuda):
     preprocess_gpu(x, torch.from_numpy(frames).to(cuda), eng.cfg.scale_input_to_net)
     net.forwardPass(x)
     out = net.getOutputBlobArray()
-    heat = torch.empty((n, 78, eng.cfg.net_h, eng.cfg.net_w), device=cuda)
+    heat = torch.empty((n, out.shape[1], eng.cfg.net_h, eng.cfg.net_w), device=cuda)
     post.resize_and_merge_gpu(heat, [out])
-    peaks = torch.zeros((n, 25, 128, 3), device=cuda)
+    peaks = torch.zeros((n, eng.parts, eng.cfg.connect.max_peaks + 1, 3), device=cuda)
     off = float(np.float32(0.5 / float(eng.cfg.connect.scale_factor)))
     post.nms_gpu(peaks, heat, eng.cfg.nms_threshold, (off, off))
     kp, sc, cnt = post.connect_body_parts_gpu(heat, peaks, eng.cfg.connect, capacity=eng.capacity)
@@ -34,11 +34,12 @@ def _reference_chain(proto, cm, frames, eng, cuda):
     return res
 
 
-def test_engine_matches_step_by_step_calls_and_keeps_frame_order(cuda):
-    proto, cm, _, _ = modelgen.build_files("body_25", 1234)
+@pytest.mark.parametrize("model,pose_model", [("body_25", 0), ("coco", 1)])
+def test_engine_matches_step_by_step_calls_and_keeps_frame_order(cuda, model, pose_model):
+    proto, cm, _, _ = modelgen.build_files(model, 1234)
     frame_size, net_size, batch = (320, 180), (160, 96), 3
-    eng = PoseEngine(proto, cm, gpus=[0], net_size=net_size, frame_size=frame_size, batch=batch, lanes=2, capacity=64,
-                     overrides=LOOSE)
+    eng = PoseEngine(proto, cm, gpus=[0], pose_model=pose_model, net_size=net_size, frame_size=frame_size, batch=batch,
+                     lanes=2, capacity=64, overrides=LOOSE)
     batches = [synth.frames(batch, frame_size[1], frame_size[0], 50 + i) for i in range(5)]
     batches[3] = batches[3][:2]                                   # a short batch in the middle
     fid = 0
