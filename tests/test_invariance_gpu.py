@@ -50,3 +50,19 @@ def test_post_processing_follows_a_permutation_of_the_batch(cuda):
         for part in range(25):
             m = int(pk0[j, part, 0, 0])
             assert np.array_equal(pk1[i, part, :m + 1], pk0[j, part, :m + 1])
+
+
+@pytest.mark.parametrize("model,hw", [("body_25", (368, 656)), ("coco", (184, 328)), ("hand", (368, 368))])
+def test_net_output_is_the_same_in_every_batch_size(cuda, model, hw):
+    """the small-batch planner changes tiles per work item, Cout tile width and CTA pairing with the batch; none of that
+    may change a bit of a frame's output"""
+    proto, cm, _, _ = modelgen.build_files(model, 1234)
+    x = torch.from_numpy(synth.frames_to_net_input(synth.frames(24, hw[0], hw[1], 33))).to(cuda)
+    net = NetB200(proto, cm)
+    net.initializationOnThread()
+    net.forwardPass(x)
+    full = net.getOutputBlobArray().clone()
+    for n in (1, 2, 3, 4, 6, 9, 16):
+        net.forwardPass(x[:n].contiguous())
+        assert torch.equal(net.getOutputBlobArray(), full[:n]), "batch %d" % n
+    net.close()
