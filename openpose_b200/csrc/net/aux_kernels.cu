@@ -341,8 +341,13 @@ namespace opb
     // per-n-tile slope / bounds handling tripled the instruction count.
     // ----------------------------------------------------------------------------------------------------
     constexpr int kF3PatchW = 34;                       // 32 pixels + the halo column either side
-    constexpr int kF3Patch = 9 * kF3PatchW;             // floats per staged patch: (channel, row) x column
-    constexpr int kF3Fill = (kF3Patch + 31) / 32;       // cp.async per lane and unit
+    // Row pitch of the staged patch, in floats. A gather instruction reads, for its four k-groups (lane & 3), taps that lie
+    // in up to three consecutive (channel, row) lines of the patch, 8 consecutive pixels each: with a pitch of 42 (= 10 mod
+    // 32) three consecutive lines start 10 banks apart and the reads are conflict-free (pitch 34: 2-way conflicts, a
+    // third of all shared-memory wavefronts of the kernel).
+    constexpr int kF3Pitch = 42;
+    constexpr int kF3Patch = 9 * kF3Pitch;              // floats per staged patch: (channel, row) x column
+    constexpr int kF3Fill = (9 * kF3PatchW + 31) / 32;  // cp.async per lane and unit
     constexpr int kF3SmemBytes = kFirstWarps * (32 * kFirstPitch + 2 * kF3Patch * 4);
 
     __device__ __forceinline__ void cpAsync4(uint32_t dstSmem, const float* src, uint32_t srcBytes)
@@ -381,7 +386,7 @@ namespace opb
         for (int e = 0; e < 8; ++e)
         {
             const int j = 16 * (e >> 2) + 2 * q + (e & 1) + ((e >> 1) & 1) * 8;
-            pOff[e] = j < 27 ? (j / 3) * kF3PatchW + j % 3 : -1;      // K padding: contributes zero
+            pOff[e] = j < 27 ? (j / 3) * kF3Pitch + j % 3 : -1;       // K padding: contributes zero
         }
         // the patch elements this lane copies per unit: i = lane + 32*m -> (channel*3 + row, column)
         int fOff[kF3Fill];          // global offset relative to the unit's first pixel, or INT_MIN past the patch
@@ -391,7 +396,7 @@ namespace opb
             const int i = lane + 32 * m;
             const int cr = i / kF3PatchW, col = i - cr * kF3PatchW;
             const int c = cr / 3, r = cr - c * 3;
-            fOff[m] = i < kF3Patch ? c * H * W + (r - 1) * W + (col - 1) : INT_MIN;
+            fOff[m] = i < 9 * kF3PatchW ? c * H * W + (r - 1) * W + (col - 1) : INT_MIN;
         }
         const int xBlocks = (W + 31) >> 5;
         const int units = N * H * xBlocks;
@@ -411,7 +416,10 @@ namespace opb
 #pragma unroll
                 for (int m = 0; m < kF3Fill; ++m)
                     if (fOff[m] != INT_MIN)
-                        cpAsync4(dstBase + (uint32_t)(lane + 32 * m) * 4u, base + fOff[m], 4u);
+                    {
+                        const int i = lane + 32 * m;       // element (line i / 34, column i % 34) -> line * pitch + column
+                        cpAsync4(dstBase + (uint32_t)(i + (i / kF3PatchW) * (kF3Pitch - kF3PatchW)) * 4u, base + fOff[m], 4u);
+                    }
             }
             else
             {
@@ -423,7 +431,7 @@ namespace opb
                         const int cr = i / kF3PatchW, col = i - cr * kF3PatchW;
                         const int yy = y + cr % 3 - 1, xx = x0 + col - 1;
                         const bool ok = yy >= 0 && yy < H && xx >= 0 && xx < W;
-                        cpAsync4(dstBase + (uint32_t)(lane + 32 * m) * 4u, ok ? base + fOff[m] : src, ok ? 4u : 0u);
+                        cpAsync4(dstBase + (uint32_t)(i + cr * (kF3Pitch - kF3PatchW)) * 4u, ok ? base + fOff[m] : src, ok ? 4u : 0u);
                     }
             }
             asm volatile("cp.async.commit_group;" ::: "memory");
