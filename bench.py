@@ -546,8 +546,28 @@ def measure_latency(args, dev, steps: int = 100):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
     net1.net.close()
-    return {"batch": 1, "ms_per_frame": round(ms, 4), "frames_per_s": round(1e3 / ms, 1), "steps": steps,
-            "what": "device-resident input, frames issued back to back on one stream"}
+    out = {"batch": 1, "ms_per_frame": round(ms, 4), "frames_per_s": round(1e3 / ms, 1), "steps": steps,
+           "what": "device-resident input, frames issued back to back on one stream"}
+    # BASELINE config 1 end to end: ONE u8 1280x720 frame in host memory -> people in host memory through the engine,
+    # nothing else in flight (host wall clock per frame: H2D, pre-processing, net, resize, nms, connector, D2H, the
+    # worker thread's hand-over)
+    from openpose_b200 import modelgen
+    from openpose_b200.engine import PoseEngine
+    proto, cm, _, _ = modelgen.build_files("body_25", 1234)
+    eng = PoseEngine(proto, cm, gpus=[dev.index or 0], net_size=(NET_W, NET_H), frame_size=(FRAME_W, FRAME_H), batch=1,
+                     lanes=1, capacity=256)
+    frame = synth.frames(1, FRAME_H, FRAME_W, 9)
+    for _ in range(10):
+        eng.submit(0, frame)
+        eng.next(copy=False)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        eng.submit(i, frame)
+        eng.next(copy=False)
+    out["e2e_ms_per_frame"] = round((time.perf_counter() - t0) * 1e3 / steps, 4)
+    out["e2e_what"] = "one u8 %dx%d frame at a time through opb200_engine_* (submit -> next), host buffers" % (FRAME_W, FRAME_H)
+    eng.close()
+    return out
 
 
 # ----------------------------------------------------------------------------------------------------
