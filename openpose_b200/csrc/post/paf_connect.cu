@@ -189,20 +189,22 @@ namespace opb
         const float* A = pk + c.t.pairTable[2 * pair] * po;
         const float* B = pk + c.t.pairTable[2 * pair + 1] * po;
         const int nA = posIntRound(A[0]), nB = posIntRound(B[0]);
-        const int t = blockIdx.x * kCandThreads + threadIdx.x;
-        if (t >= nA * nB)
-            return;
         const size_t hw = (size_t)c.h * c.w;
         const float* mapX = c.heat + ((size_t)n * c.heatChannels + c.t.parts + 1 + c.t.mapIdx[2 * pair]) * hw;
         const float* mapY = c.heat + ((size_t)n * c.heatChannels + c.t.parts + 1 + c.t.mapIdx[2 * pair + 1]) * hw;
-        const int i = t / nB + 1, j = t - (i - 1) * nB + 1;
-        const float s = pafScore<OPB200_SEMANTICS_CPU>(A + 3 * i, B + 3 * j, mapX, mapY, c);
-        if ((double)s > 1e-6) // reference: bodyPartConnectorBase.cpp:317
+        // a few blocks per (limb, frame) stride over its nA * nB pairs: a grid sized for maxPeaks^2 pairs is 64 blocks per
+        // (limb, frame), of which an 8-person frame uses one (73 216 blocks, 68 us, for 44 frames)
+        for (int t = blockIdx.x * kCandThreads + threadIdx.x; t < nA * nB; t += gridDim.x * kCandThreads)
         {
-            const size_t slot = (size_t)n * c.t.pairs + pair;
-            const int pos = atomicAdd(c.candCount + slot, 1);
-            c.candKeys[slot * mp * mp + pos] =
-                ((unsigned long long)__float_as_uint(s) << 16) | ((unsigned)i << 8) | (unsigned)j;
+            const int i = t / nB + 1, j = t - (i - 1) * nB + 1;
+            const float s = pafScore<OPB200_SEMANTICS_CPU>(A + 3 * i, B + 3 * j, mapX, mapY, c);
+            if ((double)s > 1e-6) // reference: bodyPartConnectorBase.cpp:317
+            {
+                const size_t slot = (size_t)n * c.t.pairs + pair;
+                const int pos = atomicAdd(c.candCount + slot, 1);
+                c.candKeys[slot * mp * mp + pos] =
+                    ((unsigned long long)__float_as_uint(s) << 16) | ((unsigned)i << 8) | (unsigned)j;
+            }
         }
     }
 
@@ -1005,7 +1007,8 @@ extern "C" opb200_status opb200_connect(float* out_keypoints, float* out_scores,
         c.candCount = reinterpret_cast<int*>(static_cast<unsigned char*>(scratch) + connBytes);
         c.candKeys = reinterpret_cast<unsigned long long*>(static_cast<unsigned char*>(scratch) + connBytes + countBytes);
         OPB_CUDA(cudaMemsetAsync(c.candCount, 0, sizeof(int) * (size_t)nFrames * c.t.pairs, st));
-        const dim3 grid((c.maxPeaks * c.maxPeaks + kCandThreads - 1) / kCandThreads, c.t.pairs, nFrames);
+        const int blocksX = std::min(8, (c.maxPeaks * c.maxPeaks + kCandThreads - 1) / kCandThreads);
+        const dim3 grid(blocksX, c.t.pairs, nFrames);
         pafCandKernel<<<grid, kCandThreads, 0, st>>>(c);
         OPB_LAUNCH_CHECK();
     }
