@@ -662,8 +662,9 @@ def main():
     ap.add_argument("--steps", type=int, default=100)   # 1.2 s per timed region: the sustained (power-capped) rate
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=44,
-                    help="frames per step per GPU (44 x 33 tiles of the 46x82 layers = 4.9 waves of 148 SMs x 2 tiles)")
+    ap.add_argument("--batch", type=int, default=47,
+                    help="frames per step per GPU (47 frames: the 46x82 levels are 1464 tiles = 366 quads = 4.95 waves of the 74 "
+                         "CTA pairs; 44 frames, the default until late in round 2, are 4.65 waves)")
     ap.add_argument("--people", type=int, default=8, help="planted people per frame (post-only workload)")
     ap.add_argument("--stages", default=DEFAULT_STAGES, choices=["full", "post", "net"])
     ap.add_argument("--post-input", default="planted", choices=["planted", "net"],
