@@ -243,6 +243,12 @@ opb200_status opb200_net_read_blob(opb200_net* net, const char* name, float* hos
 /* Host-only (no CUDA call): parse + plan the model and write one text line per planned kernel launch. */
 opb200_status opb200_net_describe(const char* prototxt, const char* caffemodel, const char* last_blob_name,
                                   char* text, size_t capacity);
+/* Host-only: the activation levels of the planned graph for an (n, 3, h, w) input -- size, number of convs reading the
+ * level, their widest padding, and whether the level is stored frame-interleaved and with how many zero separator columns
+ * (text lines "level L h= w= convs= max_pad= flat= sep="). No reference counterpart: it exposes the layout decision of
+ * the reshape (reference: NetCaffe::reshapeNetCaffe, src/openpose/net/netCaffe.cpp:105-122) to tests without a GPU. */
+opb200_status opb200_net_describe_shape(const char* prototxt, const char* caffemodel, const char* last_blob_name, int n,
+                                        int h, int w, char* text, size_t capacity);
 
 /* ---------------------------------------------------------------------------------------------------
  * Output serialisation -- host only, no CUDA call.

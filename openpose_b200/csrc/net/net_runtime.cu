@@ -724,22 +724,10 @@ namespace opb
         return OPB200_OK;
     }
 
-    // ------------------------------------------------------------------------------------------------
-    // reshape: level sizes, arena, tensor maps (reference: reshapeNetCaffe, netCaffe.cpp:105-122)
-    // ------------------------------------------------------------------------------------------------
-    // `own` is the net's stream (created non-blocking, so the legacy default stream does not order against it): the
-    // previous shape's work on it and on the caller's stream `user` (which may still read the old output blob) is
-    // drained before the graph and the arena are torn down, and the zero fill of the new arena is enqueued on `own`,
-    // ahead of everything the following forward puts there.
-    static opb200_status reshapeNet(Net& net, int N, int H, int W, cudaStream_t own, cudaStream_t user)
+    // Host-only part of a reshape: the size of every level for an (N, H, W) input and which levels are stored
+    // frame-interleaved, with how many separator columns (also behind opb200_net_describe_shape, for the CPU tests).
+    static void layoutLevels(Net& net, int N, int H, int W)
     {
-        OPB_CUDA(cudaStreamSynchronize(own));
-        OPB_CUDA(cudaStreamSynchronize(user));
-        if (net.graphExec)
-        {
-            cudaGraphExecDestroy(net.graphExec);
-            net.graphExec = nullptr;
-        }
         net.lvH.assign(net.levels.size(), 0);
         net.lvW.assign(net.levels.size(), 0);
         net.lvH[0] = H;
@@ -754,12 +742,6 @@ namespace opb
             net.lvH[l] = pooled(net.lvH[lv.parent]);
             net.lvW[l] = pooled(net.lvW[lv.parent]);
         }
-        size_t total = 0;
-        auto carve = [&](size_t bytes) {
-            const size_t at = total;
-            total += (bytes + 1023) / 1024 * 1024;
-            return at;
-        };
         // Flat levels (conv_params.h): only where every reader and writer of the level's buffers is the conv kernel
         // (TMA loads, TMA stores, fused pooled stores) or the fp32 converter, and where it saves M tiles.
         const bool flatEnabled = !(std::getenv("OPB200_CONV_FLAT") && std::atoi(std::getenv("OPB200_CONV_FLAT")) == 0);
@@ -795,6 +777,31 @@ namespace opb
             }
             net.lvFlat[l] = ok ? 1 : 0;
         }
+    }
+
+    // ------------------------------------------------------------------------------------------------
+    // reshape: level sizes, arena, tensor maps (reference: reshapeNetCaffe, netCaffe.cpp:105-122)
+    // ------------------------------------------------------------------------------------------------
+    // `own` is the net's stream (created non-blocking, so the legacy default stream does not order against it): the
+    // previous shape's work on it and on the caller's stream `user` (which may still read the old output blob) is
+    // drained before the graph and the arena are torn down, and the zero fill of the new arena is enqueued on `own`,
+    // ahead of everything the following forward puts there.
+    static opb200_status reshapeNet(Net& net, int N, int H, int W, cudaStream_t own, cudaStream_t user)
+    {
+        OPB_CUDA(cudaStreamSynchronize(own));
+        OPB_CUDA(cudaStreamSynchronize(user));
+        if (net.graphExec)
+        {
+            cudaGraphExecDestroy(net.graphExec);
+            net.graphExec = nullptr;
+        }
+        layoutLevels(net, N, H, W);
+        size_t total = 0;
+        auto carve = [&](size_t bytes) {
+            const size_t at = total;
+            total += (bytes + 1023) / 1024 * 1024;
+            return at;
+        };
         for (auto& b : net.buffers)
         {
             const int w = net.lvW[b.level] + (net.lvFlat[b.level] ? net.lvSep[b.level] : 0);
@@ -1293,6 +1300,49 @@ extern "C" opb200_status opb200_net_read_blob(opb200_net* n, const char* name, f
 
 // Host-only: parse + plan, no CUDA call. Writes one line per planned op into `text` (for tests and debugging):
 //   conv <name> cin cout k bn tilesN segs=[buf:off:C,...] out=buf:off:C out32=<off|-1> bf16=<0|1>
+extern "C" opb200_status opb200_net_describe_shape(const char* prototxt, const char* caffemodel, const char* last_blob_name,
+                                                   int n, int h, int w, char* text, size_t capacity)
+{
+    OPB_REQUIRE(prototxt && caffemodel && text && capacity > 0, "net_describe_shape: null argument");
+    OPB_REQUIRE(n > 0 && h > 0 && w > 0, "net_describe_shape: empty input shape");
+    Net net;
+    net.lastBlobName = (last_blob_name && *last_blob_name) ? last_blob_name : "net_output";
+    std::string src, err;
+    if (!readFile(prototxt, src) || !parsePrototxt(src, net.def, err))
+    {
+        setError("%s (%s)", err.empty() ? "prototxt: cannot read file" : err.c_str(), prototxt);
+        return OPB200_ERR_IO;
+    }
+    WeightMap wm;
+    if (!readCaffemodel(caffemodel, wm, err))
+    {
+        setError("%s", err.c_str());
+        return OPB200_ERR_IO;
+    }
+    const opb200_status s = planNet(net, wm);
+    if (s != OPB200_OK)
+        return s;
+    layoutLevels(net, n, h, w);
+    std::string out;
+    char line[256];
+    for (size_t l = 0; l < net.levels.size(); ++l)
+    {
+        int maxPad = 0, convs = 0;
+        for (const auto& op : net.ops)
+            if (op.kind == OP_CONV && op.level == (int)l)
+            {
+                ++convs;
+                maxPad = std::max(maxPad, op.pad);
+            }
+        std::snprintf(line, sizeof(line), "level %d h=%d w=%d convs=%d max_pad=%d flat=%d sep=%d\n", (int)l, net.lvH[l], net.lvW[l],
+                      convs, maxPad, net.lvFlat[l], net.lvFlat[l] ? net.lvSep[l] : 0);
+        out += line;
+    }
+    OPB_REQUIRE(out.size() + 1 <= capacity, "net_describe_shape: text buffer too small");
+    std::memcpy(text, out.c_str(), out.size() + 1);
+    return OPB200_OK;
+}
+
 extern "C" opb200_status opb200_net_describe(const char* prototxt, const char* caffemodel, const char* last_blob_name,
                                              char* text, size_t capacity)
 {

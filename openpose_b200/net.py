@@ -28,6 +28,8 @@ class NetInfo(C.Structure):
 _lib.register({
     "opb200_net_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_char_p, C.c_char_p, C.c_int, C.c_char_p]),
     "opb200_net_destroy": (None, [C.c_void_p]),
+    "opb200_net_describe_shape": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_char_p,
+                                            C.c_size_t]),
     "opb200_net_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, _lib._I4, C.c_void_p]),
     "opb200_net_output": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), _lib._I4]),
     "opb200_net_input_buffer": (C.c_int, [C.c_void_p, _lib._I4, C.POINTER(C.c_void_p), C.c_void_p]),
@@ -43,6 +45,19 @@ class _DevView:
     def __init__(self, ptr: int, shape, typestr="<f4"):
         self.__cuda_array_interface__ = {"shape": tuple(int(s) for s in shape), "typestr": typestr,
                                          "data": (int(ptr), False), "version": 3, "strides": None}
+
+
+def describe_shape(proto: str, caffemodel: str, n: int, h: int, w: int, last_blob: str = "net_output"):
+    """Host-only (no CUDA): the activation levels for an (n, 3, h, w) input as dicts with h, w, convs, max_pad, flat, sep --
+    which levels are stored frame-interleaved and with how many zero separator columns."""
+    L = _lib.lib()
+    buf = C.create_string_buffer(1 << 16)
+    _lib.check(L.opb200_net_describe_shape(proto.encode(), caffemodel.encode(), last_blob.encode(), int(n), int(h), int(w),
+                                           buf, len(buf)))
+    levels = []
+    for line in buf.value.decode().splitlines():
+        levels.append({k: int(v) for k, v in (t.split("=") for t in line.split()[2:])})
+    return levels
 
 
 def describe(proto: str, caffemodel: str, last_blob: str = "net_output") -> str:

@@ -10,7 +10,7 @@ import pytest
 import torch
 
 from openpose_b200 import net as netmod
-from openpose_b200 import protogen
+from openpose_b200 import modelgen, protogen
 from openpose_b200._lib import Opb200Error
 from oracle import caffe_io, ref_net
 
@@ -216,3 +216,27 @@ def test_prototxt_hostile_nesting_and_anisotropic_pooling(tmp_path):
                     'pooling_param { pool: MAX kernel_h: 2 kernel_w: 3 stride: 2 } }\n')
     with pytest.raises(Opb200Error, match="non-square pooling"):
         netmod.describe(str(pool), cm)
+
+
+@pytest.mark.parametrize("model,shape,level_hw,flat,sep", [
+    ("body_25", (47, 368, 656), (46, 82), 1, 1),      # 3x3 convs only: one separator column
+    ("coco", (64, 368, 656), (46, 82), 1, 3),         # 7x7 convs (pad 3) read the level: three
+    ("hand", (32, 96, 96), (12, 12), 1, 3),
+    ("face", (32, 96, 96), (12, 12), 1, 3),
+    ("hand", (16, 368, 368), (46, 46), 0, 0),         # 46 + 3 columns per frame no longer save a tile against 3 x 16
+    ("hand", (2, 96, 96), (12, 12), 0, 0),            # too few frames for the interleaved layout to save tiles
+    ("body_25", (1, 368, 656), (46, 82), 0, 0),
+])
+def test_interleaved_levels_have_separators_as_wide_as_the_padding(model, shape, level_hw, flat, sep):
+    """Frame-interleaved ("flat") levels rely on zero separator columns between frames as the horizontal padding, so a level
+    read by a conv with pad p needs p of them (regression: one column under the 7x7 layers of COCO / hand / face made their
+    filters read the neighbouring frame). Host-only, through opb200_net_describe_shape."""
+    proto, cm, _, _ = modelgen.build_files(model, 1234)
+    levels = netmod.describe_shape(proto, cm, *shape)
+    assert levels[0]["h"] == shape[1] and levels[0]["w"] == shape[2] and levels[0]["flat"] == 0
+    hits = [lv for lv in levels if (lv["h"], lv["w"]) == level_hw]
+    assert len(hits) == 1 and hits[0]["convs"] > 0
+    assert hits[0]["flat"] == flat and hits[0]["sep"] == sep
+    for lv in levels:
+        if lv["flat"]:
+            assert lv["sep"] >= max(1, lv["max_pad"])
