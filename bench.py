@@ -467,7 +467,10 @@ def run_gpu(args):
                    "batch_per_gpu": B, "stages": args.stages,
                    "l2": "inputs larger than L2: %d MB of heat-maps per step vs 126 MB L2"
                          % (B * CHANNELS * NET_H * NET_W * 4 // 2 ** 20),
-                   "sharding": "frame-sharded, no collective"},
+                   "sharding": "frame-sharded, no collective",
+                   "timed_region": "%d steps = %.2f s per region: at the default 100 steps the board sits at its power cap "
+                                   "for the whole region, so `value` and `e2e` are sustained rates (20-step regions read "
+                                   "about 5 %% higher)" % (args.steps, ms_total / 1e3)},
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / args.steps, "mode": e2e_mode},
         "gpu_launches": launches * args.steps,
