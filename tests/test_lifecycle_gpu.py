@@ -8,7 +8,8 @@ import pytest
 import torch
 
 from openpose_b200 import modelgen, synth
-from openpose_b200.engine import PoseEngine
+from openpose_b200.crop_extractors import crop_matrix
+from openpose_b200.engine import CropEngine, PoseEngine
 from openpose_b200.net import NetB200
 
 pytestmark = pytest.mark.gpu
@@ -57,6 +58,25 @@ def test_engine_create_destroy_returns_device_memory(cuda):
         b = cycle()
         assert a[0] == b[0] and all(np.array_equal(u, v) for u, v in zip(a[1:], b[1:]))
     assert base - _free_bytes() < (8 << 20), "device memory not returned by opb200_engine_destroy"
+
+
+def test_crop_engine_create_destroy_returns_device_memory(cuda):
+    proto, cm, _, _ = modelgen.build_files("hand", 4321)
+    frame = synth.frames(1, 240, 320, 5)[0]
+    mats = np.stack([crop_matrix((40.0, 30.0, 120.0, 120.0), 96, False), crop_matrix((150.0, 60.0, 90.0, 90.0), 96, True)])
+
+    def cycle():
+        eng = CropEngine(proto, cm, 22, gpus=[0], frame_size=(320, 240), net_side=96, batch=2, lanes=2)
+        eng.submit(0, frame, mats)
+        res = eng.next()[1]
+        eng.close()
+        return res
+
+    a = cycle()
+    base = _free_bytes()
+    for _ in range(3):
+        assert np.array_equal(cycle(), a)
+    assert base - _free_bytes() < (8 << 20), "device memory not returned by opb200_engine_destroy (crop mode)"
 
 
 def test_two_nets_on_two_host_threads(cuda):
