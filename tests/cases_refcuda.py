@@ -44,3 +44,7 @@ def max_input(c, h, w, seed):
 
 def pre_input(hs, ws, seed):
     return np.random.default_rng(seed).integers(0, 256, size=(hs, ws, 3), dtype=np.uint8)
+
+
+# connectBodyPartsGpu: indices into tests.cases.POST_CASES (small maps: the fixture stays small)
+CONNECT_CASES = [7, 6]    # BODY_25 46x82 with 2 people, BODY_25 184x328 with 5 people

@@ -47,6 +47,23 @@ def main():
         res = ref.preprocess(torch.from_numpy(frame).to(dev), net, scale)
         out["pre/%s/crc" % name] = crc(frame)
         out["pre/%s/out" % name] = res.cpu().numpy()
+    from oracle.post import MODE_CUDA, Port, model_dims, pose_defaults
+    from tests.cases import POST_CASES, case_id, make_case
+    port = Port()
+    for ci in K.CONNECT_CASES:
+        case = POST_CASES[ci]
+        model = case[0]
+        parts = model_dims(model)[0]
+        maps, _ = make_case(case)
+        peaks = port.nms(maps, 0.05, parts, off=(0.25, 0.25), mode=MODE_CUDA)      # the same peaks on both sides
+        cid = case_id(case)
+        out["connect/%s/crc" % cid] = crc(maps)
+        for mp in (0, 1):
+            kp, sc, cube = ref.connect(torch.from_numpy(maps).to(dev), torch.from_numpy(peaks).to(dev), model,
+                                       p=pose_defaults(model, bool(mp)), scale=1.959, maximize_positives=bool(mp))
+            out["connect/%s/kp%d" % (cid, mp)] = kp
+            out["connect/%s/sc%d" % (cid, mp)] = sc
+            out["connect/%s/cube%d" % (cid, mp)] = cube        # mostly zeros: compresses to a few KB
     path = out_path
     np.savez_compressed(path, **out)
     print("wrote", path, os.path.getsize(path) // 1024, "KiB,", len(out), "arrays")

@@ -56,3 +56,25 @@ def test_preprocess_contracted_matches_reference_kernels(port, golden, case):
     frame = K.pre_input(hs, ws, seed)
     assert _crc(frame) == int(golden["pre/%s/crc" % name][0]), "generator drifted"
     assert np.array_equal(port.preprocess(frame, net, scale, contract=True), golden["pre/%s/out" % name])
+
+
+@pytest.mark.parametrize("ci", K.CONNECT_CASES)
+def test_connect_cuda_semantics_matches_reference_kernels(port, golden, ci):
+    """pafScoreKernel's cube (process() with nvcc's FMA contraction) and connectBodyPartsGpu's people."""
+    from oracle.post import model_dims, pose_defaults
+    from tests.cases import POST_CASES, case_id, make_case
+    case = POST_CASES[ci]
+    model = case[0]
+    parts = model_dims(model)[0]
+    maps, _ = make_case(case)
+    cid = case_id(case)
+    if "connect/%s/crc" % cid not in golden:
+        pytest.skip("fixture generated before the connector cases were added")
+    assert _crc(maps) == int(golden["connect/%s/crc" % cid][0]), "generator drifted"
+    peaks = port.nms(maps, 0.05, parts, off=(0.25, 0.25), mode=MODE_CUDA)
+    for mp in (0, 1):
+        cube = port.pair_scores(maps, peaks, model, p=pose_defaults(model, bool(mp)), mode=MODE_CUDA)
+        assert np.array_equal(cube, golden["connect/%s/cube%d" % (cid, mp)])
+        res = port.connect_from_pair_scores(cube, peaks, model, scale=1.959, maximize_positives=bool(mp))
+        assert np.array_equal(res[0], golden["connect/%s/kp%d" % (cid, mp)])
+        assert np.array_equal(res[1], golden["connect/%s/sc%d" % (cid, mp)])
